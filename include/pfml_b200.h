@@ -1,0 +1,122 @@
+/* pfml_b200.h -- C ABI of libpfml_b200.so: the Portfolio-ML (PFML) hot path of the JKMP22 replication,
+ * hand-written for NVIDIA B200 (sm_100a).
+ *
+ * The reference (brockpat/JKMP22-...-Replication) is pure Python and has no FFI; its boundary is the set of
+ * importable functions and scripts listed below.  Each entry point here replaces the arithmetic of one of
+ * them; the Python host mirror (package `..._b200`, alias `pfml_b200`) keeps the reference's names and
+ * argument meaning and calls these through ctypes.
+ *
+ * Conventions
+ *   - every tensor is caller-owned, contiguous, row-major IEEE FP64 in DEVICE memory unless the name says
+ *     `_host`; index arrays are int32;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are asynchronous on it;
+ *   - no hidden allocation: the caller passes a workspace whose size the matching *_workspace_bytes query
+ *     returns (the *_host convenience entry points allocate and free their own device buffers);
+ *   - return value: 0 ok; <0 bad argument / CUDA error (text via pfml_last_error()); numerical failures are
+ *     reported per date in the `status` array (bit 0: singular pivot in a block inverse, bit 1: matrix
+ *     square root did not converge / non-finite input);
+ *   - never throws, never exits; thread-safe per stream.
+ */
+#ifndef PFML_B200_H
+#define PFML_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* pfml_version(void);
+const char* pfml_last_error(void);
+
+/* Device-resident panel for a block of consecutive months t = 0..T-1 (dense: row index = t*N + i). */
+typedef struct {
+  int T, N, F, p, K;        /* months, stocks, characteristics, RFF features (cos+sin), factors (K <= 32) */
+  const double* rff;        /* [T*N][p]  [cos | sin], output of pfml_rff_sincos  (PFML_Input_Data.py:254) */
+  const double* vol_scale;  /* [T*N]     sqrt(diag(Sigma)) with eom-median fill   (PFML_Input_Data.py:274-305) */
+  const double* gt;         /* [T*N]     (1+tr_ld0)/(1+mu_ld0), NaN where missing (PFML_Input_Data.py:404,:458) */
+  const double* lam;        /* [T*N]     Kyle's lambda                            (PFML_Input_Data.py:116-120) */
+  const double* ret_ld1;    /* [T*N]     lead returns                             (PFML_Input_Data.py:330) */
+  const double* fct_load;   /* [T*N][K]  Barra loadings                           (Barra_Cov.pkl 'fct_load') */
+  const double* fct_cov;    /* [T][K][K] factor covariance                        (Barra_Cov.pkl 'fct_cov') */
+  const double* ivol;       /* [T*N]     idiosyncratic variance                   (Barra_Cov.pkl 'ivol_vec') */
+  const double* wealth;     /* [T]       (wealth_processed.csv) */
+  const double* rf;         /* [T]       decimal risk-free rate (FF_RF_monthly.csv / 100) */
+  double gamma_rel, mu;     /* pf_set['gamma_rel'], pf_set['mu']  (General_functions.py:103-108) */
+  int lb, iterations;       /* pf_set['lb_hor'] = 11; iterations = 10 (PFML_Input_Data.py:215) */
+} pfml_panel_t;
+
+/* a1 -- random Fourier features.  Replaces rff(X, W=W) + the [cos | sin] concatenation,
+ * PFML_Input_Data.py:159-185, :254.  X [rows][F], W [F][p_half] -> out [rows][2*p_half]. */
+int pfml_rff_sincos(const double* X, const double* W, long rows, int F, int p_half, double* out, void* stream);
+
+/* a2 -- vol_scale = sqrt(diag(L F L' + diag(ivol))) per (month, stock) without forming Sigma, NaN where
+ * `has` is 0, then the per-month median fill.  Replaces PFML_Input_Data.py:274-305 (create_cov + diag,
+ * General_functions.py:869).  has may be NULL (all present). */
+int pfml_vol_scale(const double* fct_load, const double* fct_cov, const double* ivol, const unsigned char* has,
+                   int T, int N, int K, double* vol_scale, void* stream);
+
+/* g_t = (1 + tr_ld0) / (1 + mu_ld0) per (month, stock), NaN kept (PFML_Input_Data.py:404, :458). */
+int pfml_growth_ratio(const double* tr_ld0, const double* mu_ld0, long n, double* gt, void* stream);
+
+/* a3..a9 -- B date-steps of the loop PFML_Input_Data.py:318-491 (create_cov :333, create_lambda :336,
+ * m_func :345, standardise/scale :357-388, gtm chains :400-429, omega :438-462, r_tilde/risk/tc/denom
+ * :470-481), one per entry of date_t.  sel [B][NP] holds the stock indices (ascending ids) of each date's
+ * universe, n_sel [B] their count, NP = pfml_padded_n(n_max).  Outputs are in feat_all order
+ * (constant, cos 1..p/2, sin 1..p/2; PFML_Input_Data.py:221,:484,:489), P = p + 1:
+ *   r_tilde [B][P], denom/risk/tc [B][P][P], signal_t [B][NP][P] (rows >= n_sel[b] are zero).
+ * risk, tc, signal_t may be NULL.  status [B] int32 (may be NULL) receives numerical-failure bits. */
+int pfml_padded_n(int n_max);
+size_t pfml_date_steps_workspace_bytes(const pfml_panel_t* panel, int B, int n_max);
+int pfml_date_steps(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                    double* r_tilde, double* denom, double* risk, double* tc, double* signal_t, int* status,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
+/* a5 -- m_func(w, mu, rf, sigma_gam, gam, K_Lambda, iterations), General_functions.py:919-962, batched over
+ * B problems of equal size n: sigma_gam [B][n][n], lam [B][n] (diagonal of K_Lambda), w [B], rf [B] -> m [B][n][n]. */
+size_t pfml_mfunc_workspace_bytes(int B, int n);
+int pfml_mfunc_batched(int B, int n, const double* sigma_gam, const double* lam, const double* w, const double* rf,
+                       double mu, double gam, int iterations, double* m_out, int* status, void* workspace,
+                       size_t workspace_bytes, void* stream);
+
+/* General batched FP64 GEMM on the DMMA pipe, D = alpha * op(A) op(B) + beta * D0 (the reference's `@`):
+ * trans_a/trans_b = 0: stored [M][K] / [K][N]; 1: stored transposed.  Batch strides in elements. */
+int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alpha, const double* A, long lda, long sA,
+                       const double* B, long ldb, long sB, double beta, double* D, long ldd, long sD, int batch,
+                       void* stream);
+
+/* Batched inverse of well-conditioned n x n matrices by recursive Schur-complement blocks (np.linalg.inv at
+ * General_functions.py:960).  A [B][n][n] -> Ainv [B][n][n]. */
+size_t pfml_inverse_workspace_bytes(int B, int n);
+int pfml_inverse_batched(int B, int n, const double* A, double* Ainv, int* status, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
+/* Whole block through HOST buffers (the end-to-end call a drop-in user makes): uploads the block's inputs,
+ * runs a1 + a2 + B date-steps on the device, downloads the outputs.  feats [T*N][F], W [F][p/2], tr_ld0/
+ * mu_ld0/lam/ret_ld1/ivol [T*N], fct_load [T*N][K], fct_cov [T][K][K], barra_has [T*N] (uint8, may be NULL),
+ * wealth/rf [T]; date_t/sel/n_sel as above but in host memory.  Output pointers are host memory (pinned
+ * memory gives asynchronous copies); risk, tc, signal_t may be NULL. */
+typedef struct {
+  int T, N, F, p, K;
+  const double *feats, *W, *tr_ld0, *mu_ld0, *lam, *ret_ld1, *fct_load, *fct_cov, *ivol, *wealth, *rf;
+  const unsigned char* barra_has;
+  double gamma_rel, mu;
+  int lb, iterations;
+} pfml_host_block_t;
+int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_max, const int* date_t, const int* sel,
+                         const int* n_sel, double* r_tilde, double* denom, double* risk, double* tc,
+                         double* signal_t, int* status, int chunk, int device);
+
+/* Device-time accounting with CUDA events (used by bench.py for the live roofline): enable, run, collect.
+ * pfml_prof_collect synchronises the device, fills ms/flops/launches [n_tags] and clears the log.
+ * Tag 0 = all DMMA GEMM launches; tags 1.. = pipeline stages (see pfml_prof_tag_name). */
+void pfml_prof_enable(int on);
+int pfml_prof_ntags(void);
+const char* pfml_prof_tag_name(int tag);
+int pfml_prof_collect(double* ms, double* flops, double* launches);
+long pfml_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PFML_B200_H */

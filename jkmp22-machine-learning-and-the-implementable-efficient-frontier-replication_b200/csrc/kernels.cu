@@ -1,0 +1,644 @@
+// Non-GEMM kernels of the PFML date-step: gathers, standardisation, element-wise matrix updates, the
+// 64x64 base-block inversion of the recursive block inverse, reductions.  All FP64, all HBM/L2-bound:
+// threads run along the contiguous (column) axis so every warp access is a full 256-byte row segment.
+#include "kernels.cuh"
+
+namespace pfml {
+
+namespace {
+
+__device__ __forceinline__ double nan_to_one(double v) { return isnan(v) ? 1.0 : v; }
+
+// ------------------------------------------------------------------------------------------------
+// per-date vectors (PFML_Input_Data.py:321-342, :404-405, :458; General_functions.py:948)
+// ------------------------------------------------------------------------------------------------
+__global__ void prep_vectors_kernel(PanelView pv, int NP, const int* __restrict__ date_t, const int* __restrict__ sel,
+                                    const int* __restrict__ nsel, BatchVecs v) {
+  const int b = blockIdx.x;
+  const int t = date_t[b], n = nsel[b];
+  const int nt = pv.lb + 2;
+  const double w = pv.wealth[t];
+  if (threadIdx.x == 0) {
+    double* sc = v.scal + (long)b * NSCAL;
+    sc[0] = w;
+    sc[1] = 1.0 / w;
+    sc[2] = 1.0 + pv.rf[t] + pv.mu;
+    sc[3] = pv.gamma_rel;
+  }
+  for (int e = threadIdx.x; e < KP * KP; e += blockDim.x) {
+    int a = e / KP, c = e % KP;
+    v.Fg[(long)b * KP * KP + e] = (a < pv.K && c < pv.K) ? pv.gamma_rel * pv.fct_cov[((long)t * pv.K + a) * pv.K + c] : 0.0;
+  }
+  for (int i = threadIdx.x; i < NP; i += blockDim.x) {
+    const long o = (long)b * NP + i;
+    if (i < n) {
+      const int s = sel[(long)b * NP + i];
+      const long row = (long)t * pv.N + s;
+      const double lam = pv.lam[row];
+      const double isl = 1.0 / sqrt(lam);
+      v.sl[o] = sqrt(lam);
+      v.isl[o] = isl;
+      for (int tau = 0; tau < nt; tau++) v.g[((long)b * nt + tau) * NP + i] = nan_to_one(pv.gt[(long)(t - tau) * pv.N + s]);
+      v.g0raw[o] = pv.gt[row];
+      v.rv[o] = isl * pv.ret_ld1[row];
+      v.dvl[o] = pv.gamma_rel * pv.ivol[row] / lam;
+    } else {
+      v.sl[o] = 1.0;
+      v.isl[o] = 1.0;
+      for (int tau = 0; tau < nt; tau++) v.g[((long)b * nt + tau) * NP + i] = 1.0;
+      v.g0raw[o] = 1.0;
+      v.rv[o] = 0.0;
+      v.dvl[o] = 0.0;
+    }
+  }
+  // gathered loadings, L @ F and lambda^-1/2 L
+  const double* F = pv.fct_cov + (long)t * pv.K * pv.K;
+  for (int e = threadIdx.x; e < NP * KP; e += blockDim.x) {
+    const int i = e / KP, c = e % KP;
+    const long o = ((long)b * NP + i) * KP + c;
+    double lg = 0.0, lf = 0.0, lt = 0.0;
+    if (i < n && c < pv.K) {
+      const int s = sel[(long)b * NP + i];
+      const double* Lrow = pv.fct_load + ((long)t * pv.N + s) * pv.K;
+      lg = Lrow[c];
+      for (int a = 0; a < pv.K; a++) lf += Lrow[a] * F[(long)a * pv.K + c];
+      lt = lg / sqrt(pv.lam[(long)t * pv.N + s]);
+    }
+    v.Lg[o] = lg;
+    v.LF[o] = lf;
+    v.Lt[o] = lt;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// x, sigma_gr, y of m_func (General_functions.py:944-955) from the factor form of Sigma (:869).
+// Padded rows/cols (i >= n) are decoupled dummy stocks: x_ii = 1, sigma_gr_ii = 1, off-diagonals 0.
+// ------------------------------------------------------------------------------------------------
+__global__ void build_x_factor_kernel(PanelView pv, int NP, const int* __restrict__ date_t, const int* __restrict__ sel,
+                                      const int* __restrict__ nsel, BatchVecs v, double* __restrict__ x,
+                                      double* __restrict__ sgr, double* __restrict__ yv) {
+  __shared__ double sLF[32][KP + 1];
+  __shared__ double sL[32][KP + 1];
+  const int b = blockIdx.z, i0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+  const int n = nsel[b], t = date_t[b];
+  const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+  for (int e = ty * 32 + tx; e < 32 * KP; e += 256) {
+    int r = e / KP, c = e % KP;
+    sLF[r][c] = v.LF[((long)b * NP + i0 + r) * KP + c];
+    sL[r][c] = v.Lg[((long)b * NP + j0 + r) * KP + c];
+  }
+  __syncthreads();
+  const double* sc = v.scal + (long)b * NSCAL;
+  const double iw = sc[1], mubar = sc[2], gam = sc[3];
+  const double cs = 1.0 / (mubar * mubar);
+  const int j = j0 + tx;
+  for (int r = ty; r < 32; r += 8) {
+    const int i = i0 + r;
+    double sig = 0.0;
+#pragma unroll
+    for (int c = 0; c < KP; c++) sig += sLF[r][c] * sL[tx][c];
+    double xv, sv;
+    if (i < n && j < n) {
+      if (i == j) sig += pv.ivol[(long)t * pv.N + sel[(long)b * NP + i]];
+      const double sg = sig * gam;
+      xv = (iw * v.isl[(long)b * NP + i]) * sg * v.isl[(long)b * NP + j];
+      sv = cs * (mubar * mubar + sg / gam);
+    } else {
+      xv = (i == j) ? 1.0 : 0.0;
+      sv = (i == j) ? 1.0 : 0.0;
+    }
+    x[((long)b * NP + i) * NP + j] = xv;
+    sgr[((long)b * NP + i) * NP + j] = sv;
+    if (i == j) yv[(long)b * NP + i] = 1.0 + sv;
+  }
+}
+
+__global__ void build_x_dense_kernel(int n, int NP, const double* __restrict__ sigma_gam, const double* __restrict__ lam,
+                                     const double* __restrict__ w, const double* __restrict__ rf, double mu, double gam,
+                                     double* __restrict__ x, double* __restrict__ sgr, double* __restrict__ yv,
+                                     double* __restrict__ isl_o, double* __restrict__ sl_o) {
+  const int b = blockIdx.z;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= NP) return;
+  const double mubar = 1.0 + rf[b] + mu;
+  const double cs = 1.0 / (mubar * mubar);
+  double xv, sv;
+  if (i < n && j < n) {
+    const double sg = sigma_gam[((long)b * n + i) * n + j];
+    const double li = lam[(long)b * n + i], lj = lam[(long)b * n + j];
+    xv = ((1.0 / w[b]) * (1.0 / sqrt(li))) * sg * (1.0 / sqrt(lj));
+    sv = cs * (mubar * mubar + sg / gam);
+  } else {
+    xv = (i == j) ? 1.0 : 0.0;
+    sv = (i == j) ? 1.0 : 0.0;
+  }
+  x[((long)b * NP + i) * NP + j] = xv;
+  sgr[((long)b * NP + i) * NP + j] = sv;
+  if (i == j) {
+    yv[(long)b * NP + i] = 1.0 + sv;
+    const double l = i < n ? lam[(long)b * n + i] : 1.0;
+    isl_o[(long)b * NP + i] = 1.0 / sqrt(l);
+    sl_o[(long)b * NP + i] = sqrt(l);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Standardise + scale (PFML_Input_Data.py:357-388) for every (date, tau): de-mean each RFF column over the
+// date-d universe (two passes: mean, then sum of squares of the centred column, quirk Q6), l2-normalise,
+// multiply rows by 1/vol_scale, then by sqrt(lambda_i) (tilde domain) and, for tau in 2..lb, by g_{tau-1}
+// (pre-scaled Horner addend).  Output columns are in feat_all order: constant first (quirk Q3/Q4).
+// One thread per output column, rows streamed; the slab stays L2-resident between the three passes.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+standardize_kernel(PanelView pv, int NP, int P, long ldP, const int* __restrict__ date_t, const int* __restrict__ sel,
+                   const int* __restrict__ nsel, BatchVecs v, double* __restrict__ St, double* __restrict__ signal_t) {
+  const int b = blockIdx.z, tau = blockIdx.y;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;   // output column (0 = constant)
+  const int n = nsel[b], t = date_t[b] - tau;
+  const int nt = pv.lb + 2;
+  extern __shared__ int s_sel[];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s_sel[i] = sel[(long)b * NP + i];
+  __syncthreads();
+  if (j >= P) return;
+  const double* __restrict__ X = pv.rff + (long)t * pv.N * pv.p + (j > 0 ? j - 1 : 0);
+  double mean = 0.0, scale;
+  if (j == 0) {
+    scale = sqrt(1.0 / (double)n);                        // constant: not de-meaned, sum of squares = n
+  } else {
+    double sum = 0.0;
+#pragma unroll 8
+    for (int i = 0; i < n; i++) sum += X[(long)s_sel[i] * pv.p];
+    mean = sum / (double)n;
+    double ss = 0.0;
+#pragma unroll 8
+    for (int i = 0; i < n; i++) {
+      double c = X[(long)s_sel[i] * pv.p] - mean;
+      ss += c * c;
+    }
+    scale = sqrt(1.0 / ss);
+  }
+  const double* __restrict__ vs = pv.vol_scale + (long)t * pv.N;
+  const double* __restrict__ slb = v.sl + (long)b * NP;
+  const double* __restrict__ gprev = (tau >= 2 && tau <= pv.lb) ? v.g + ((long)b * nt + (tau - 1)) * NP : nullptr;
+  double* __restrict__ out = St + (((long)b * nt + tau) * NP) * ldP + j;
+  double* __restrict__ sig = (tau == 0 && signal_t) ? signal_t + (long)b * NP * P + j : nullptr;
+#pragma unroll 4
+  for (int i = 0; i < n; i++) {
+    const int s = s_sel[i];
+    const double c = (j == 0) ? 1.0 : X[(long)s * pv.p] - mean;
+    const double sv = (1.0 / vs[s]) * (c * scale);
+    if (sig) sig[(long)i * P] = sv;
+    double tv = slb[i] * sv;
+    if (gprev) tv *= gprev[i];
+    out[(long)i * ldP] = tv;
+  }
+  for (int i = n; i < NP; i++) {
+    out[(long)i * ldP] = 0.0;
+    if (sig) sig[(long)i * P] = 0.0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// element-wise helpers on [B][NP][NP]
+// ------------------------------------------------------------------------------------------------
+__global__ void copy2_kernel(long n, const double* __restrict__ src, double* __restrict__ d1, double* __restrict__ d2) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    double v = src[i];
+    d1[i] = v;
+    if (d2) d2[i] = v;
+  }
+}
+
+__global__ void add_kernel(long n, const double* __restrict__ a, const double* __restrict__ b, double* __restrict__ out) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) out[i] = a[i] + b[i];
+}
+
+// partial Frobenius sums of M, Mi and M - I over a chunk of rows; deterministic two-stage reduction
+__global__ void db_norms_partial_kernel(int NP, const double* __restrict__ M, const double* __restrict__ Mi, double* __restrict__ part) {
+  const int b = blockIdx.y, ch = blockIdx.x;
+  const int rows_per = (NP + NORM_CHUNKS - 1) / NORM_CHUNKS;
+  const int r0 = ch * rows_per, r1 = min(NP, r0 + rows_per);
+  double s0 = 0, s1 = 0, s2 = 0;
+  for (int r = r0; r < r1; r++) {
+    const double* m = M + ((long)b * NP + r) * NP;
+    const double* mi = Mi + ((long)b * NP + r) * NP;
+    for (int c = threadIdx.x; c < NP; c += blockDim.x) {
+      double a = m[c], q = mi[c], d = a - (r == c ? 1.0 : 0.0);
+      s0 += a * a;
+      s1 += q * q;
+      s2 += d * d;
+    }
+  }
+  __shared__ double red[3][256];
+  red[0][threadIdx.x] = s0; red[1][threadIdx.x] = s1; red[2][threadIdx.x] = s2;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) {
+      red[0][threadIdx.x] += red[0][threadIdx.x + o];
+      red[1][threadIdx.x] += red[1][threadIdx.x + o];
+      red[2][threadIdx.x] += red[2][threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x < 3) part[((long)b * NORM_CHUNKS + ch) * 3 + threadIdx.x] = red[threadIdx.x][0];
+}
+
+// Frobenius-norm scaling of the product-form Denman-Beavers iteration (Higham, Functions of Matrices, 6.29):
+//   mu = (||M^-1||_F / ||M||_F)^(1/4), switched off (mu = 1) once ||M - I||_F < 1e-2.
+// sc: 0 alpha = 0.5/mu, 1 beta = 0.5*mu, 2 mu^2, 3 1/mu^2, 4 ||M-I||_F (before this update)
+__global__ void db_norms_final_kernel(int B, const double* __restrict__ part, double* __restrict__ sc) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  double s0 = 0, s1 = 0, s2 = 0;
+  for (int ch = 0; ch < NORM_CHUNKS; ch++) {
+    s0 += part[((long)b * NORM_CHUNKS + ch) * 3 + 0];
+    s1 += part[((long)b * NORM_CHUNKS + ch) * 3 + 1];
+    s2 += part[((long)b * NORM_CHUNKS + ch) * 3 + 2];
+  }
+  const double res = sqrt(s2);
+  double mu = 1.0;
+  if (res >= 1e-2) mu = sqrt(sqrt(sqrt(s1) / sqrt(s0)));
+  double* o = sc + (long)b * 8;
+  o[0] = 0.5 / mu;
+  o[1] = 0.5 * mu;
+  o[2] = mu * mu;
+  o[3] = 1.0 / (mu * mu);
+  o[4] = res;
+}
+
+__global__ void db_update_M_kernel(int NP, double* __restrict__ M, const double* __restrict__ Mi, double* __restrict__ Wk,
+                                   const double* __restrict__ sc) {
+  const int b = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= NP) return;
+  const double mu2 = sc[(long)b * 8 + 2], imu2 = sc[(long)b * 8 + 3];
+  const long o = ((long)b * NP + r) * NP + c;
+  const double v = 0.5 * ((r == c ? 1.0 : 0.0) + 0.5 * (mu2 * M[o] + imu2 * Mi[o]));
+  M[o] = v;
+  Wk[o] = v;
+}
+
+// m_tilde_0 = 0.5 (sigma_hat - sqrtm(sigma_hat^2 - 4I)), sigma_hat = x + 2I  (General_functions.py:955-956)
+__global__ void mt0_kernel(int NP, const double* __restrict__ x, const double* __restrict__ Y, double* __restrict__ mt) {
+  const int b = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= NP) return;
+  const long o = ((long)b * NP + r) * NP + c;
+  mt[o] = 0.5 * ((x[o] + (r == c ? 2.0 : 0.0)) - Y[o]);
+}
+
+// x + y - m_tilde o sigma_gr (Hadamard)  (General_functions.py:960)
+__global__ void fp_build_kernel(int NP, const double* __restrict__ x, const double* __restrict__ yv, const double* __restrict__ mt,
+                                const double* __restrict__ sgr, double* __restrict__ Wk) {
+  const int b = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= NP) return;
+  const long o = ((long)b * NP + r) * NP + c;
+  double v = x[o];
+  if (r == c) v += yv[(long)b * NP + r];
+  Wk[o] = v - mt[o] * sgr[o];
+}
+
+// B_1 = m_tilde G_1 (column scaling) and CB = I + B_1
+__global__ void chain_init_kernel(int NP, const double* __restrict__ mt, const double* __restrict__ g1, long sg,
+                                  double* __restrict__ Bt, double* __restrict__ CB) {
+  const int b = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= NP) return;
+  const long o = ((long)b * NP + r) * NP + c;
+  const double v = mt[o] * g1[(long)b * sg + c];
+  Bt[o] = v;
+  CB[o] = v + (r == c ? 1.0 : 0.0);
+}
+
+__global__ void row_scale_kernel(int rows, int cols, long ld, long stride, const double* __restrict__ in,
+                                 const double* __restrict__ rsv, long srs, double* __restrict__ out, long ldo, long stride_o) {
+  const int b = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  out[(long)b * stride_o + (long)r * ldo + c] = rsv[(long)b * srs + r] * in[(long)b * stride + (long)r * ld + c];
+}
+
+// m = Lambda^-1/2 m_tilde Lambda^1/2 (General_functions.py:962), compact n x n output
+__global__ void m_from_mtilde_kernel(int n, int NP, const double* __restrict__ mt, const double* __restrict__ isl,
+                                     const double* __restrict__ sl, double* __restrict__ m_out) {
+  const int b = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  m_out[((long)b * n + r) * n + c] = isl[(long)b * NP + r] * mt[((long)b * NP + r) * NP + c] * sl[(long)b * NP + c];
+}
+
+// ------------------------------------------------------------------------------------------------
+// In-place Gauss-Jordan inverse with partial (row) pivoting of one 64x64 diagonal block per CTA.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+base_inverse_kernel(int NP, const double* __restrict__ src, double* __restrict__ dst, int off, int* __restrict__ status) {
+  __shared__ double a[BASE][BASE + 1];
+  __shared__ double prow[BASE], pcol[BASE];
+  __shared__ int piv[BASE];
+  __shared__ int bad;
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const double* S = src + (long)b * NP * NP + (long)off * NP + off;
+  double* Dp = dst + (long)b * NP * NP + (long)off * NP + off;
+  if (tid == 0) bad = 0;
+  for (int e = tid; e < BASE * BASE; e += 256) a[e / BASE][e % BASE] = S[(long)(e / BASE) * NP + (e % BASE)];
+  __syncthreads();
+  const int ri = tid >> 2, c0 = (tid & 3) * 16;
+  for (int k = 0; k < BASE; k++) {
+    if (tid < 32) {
+      double best = -1.0;
+      int bi = k;
+      for (int r = k + tid; r < BASE; r += 32) {
+        double v = fabs(a[r][k]);
+        if (v > best) { best = v; bi = r; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+      }
+      if (tid == 0) {
+        piv[k] = bi;
+        if (!(best > 0.0) || !isfinite(best)) bad = 1;
+      }
+    }
+    __syncthreads();
+    const int p = piv[k];
+    if (p != k && tid < BASE) {
+      double tmp = a[k][tid];
+      a[k][tid] = a[p][tid];
+      a[p][tid] = tmp;
+    }
+    __syncthreads();
+    if (tid < BASE) {
+      const double ip = 1.0 / a[k][k];
+      prow[tid] = (tid == k) ? ip : a[k][tid] * ip;
+      pcol[tid] = a[tid][k];
+    }
+    __syncthreads();
+    if (ri == k) {
+#pragma unroll
+      for (int c = 0; c < 16; c++) a[k][c0 + c] = prow[c0 + c];
+    } else {
+      const double f = pcol[ri];
+#pragma unroll
+      for (int c = 0; c < 16; c++) {
+        const int cc = c0 + c;
+        const double old = (cc == k) ? 0.0 : a[ri][cc];
+        a[ri][cc] = old - f * prow[cc];
+      }
+    }
+    __syncthreads();
+  }
+  for (int k = BASE - 1; k >= 0; k--) {
+    const int p = piv[k];
+    if (p != k && tid < BASE) {
+      double tmp = a[tid][k];
+      a[tid][k] = a[tid][p];
+      a[tid][p] = tmp;
+    }
+    __syncthreads();
+  }
+  for (int e = tid; e < BASE * BASE; e += 256) Dp[(long)(e / BASE) * NP + (e % BASE)] = a[e / BASE][e % BASE];
+  if (tid == 0 && bad && status) atomicOr(status + b, 1);
+}
+
+// out[c] = sum_r A[r][c] v[r]   (r_tilde = omega^T r, PFML_Input_Data.py:470)
+__global__ void gemv_t_kernel(int rows, int cols, const double* __restrict__ A, long ld, long sA, const double* __restrict__ v,
+                              long sv, double* __restrict__ out, long so) {
+  const int b = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  const double* a = A + (long)b * sA + c;
+  const double* vv = v + (long)b * sv;
+  double s = 0.0;
+#pragma unroll 8
+  for (int r = 0; r < rows; r++) s += a[(long)r * ld] * vv[r];
+  out[(long)b * so + c] = s;
+}
+
+__global__ void check_status_kernel(int B, const double* __restrict__ sc, int* __restrict__ status) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const double res = sc[(long)b * 8 + 4];
+  if (!(res < 1e-9)) atomicOr(status + b, 2);   // Denman-Beavers did not converge (or NaN input)
+}
+
+// g_t = (1 + tr_ld0) / (1 + mu_ld0)  (PFML_Input_Data.py:404, :458); NaN propagates
+__global__ void gt_kernel(long n, const double* __restrict__ tr, const double* __restrict__ mu, double* __restrict__ gt) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) gt[i] = (1.0 + tr[i]) / (1.0 + mu[i]);
+}
+
+// vol_scale = sqrt(diag(L F L' + diag(ivol))) (PFML_Input_Data.py:278-281) without forming Sigma; NaN if absent
+__global__ void vol_scale_kernel(const double* __restrict__ L, const double* __restrict__ F, const double* __restrict__ ivol,
+                                 const unsigned char* __restrict__ has, int N, int K, double* __restrict__ vs) {
+  const int t = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  extern __shared__ double sF[];
+  for (int e = threadIdx.x; e < K * K; e += blockDim.x) sF[e] = F[(long)t * K * K + e];
+  __syncthreads();
+  if (i >= N) return;
+  const long row = (long)t * N + i;
+  if (has && !has[row]) {
+    vs[row] = __longlong_as_double(0x7ff8000000000000LL);
+    return;
+  }
+  const double* l = L + row * K;
+  double q = 0.0;
+  for (int c = 0; c < K; c++) {
+    double lf = 0.0;
+    for (int a = 0; a < K; a++) lf += l[a] * sF[a * K + c];
+    q += lf * l[c];
+  }
+  vs[row] = sqrt(q + ivol[row]);
+}
+
+// per-month median (skipna) of vol_scale, written into the NaN slots (PFML_Input_Data.py:303-305).
+// One CTA per month; bitonic sort of the month's values in shared memory (NaN -> +inf).
+__global__ void median_fill_kernel(int N, int NPOW, double* __restrict__ vs) {
+  extern __shared__ double sv[];
+  const int t = blockIdx.x;
+  double* v = vs + (long)t * N;
+  __shared__ int n_nan;
+  if (threadIdx.x == 0) n_nan = 0;
+  __syncthreads();
+  int local = 0;
+  for (int i = threadIdx.x; i < NPOW; i += blockDim.x) {
+    double x = i < N ? v[i] : INFINITY;
+    if (i < N && isnan(x)) { x = INFINITY; local++; }
+    sv[i] = x;
+  }
+  if (local) atomicAdd(&n_nan, local);
+  __syncthreads();
+  if (n_nan == 0) return;
+  for (int k = 2; k <= NPOW; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < NPOW; i += blockDim.x) {
+        int ixj = i ^ j;
+        if (ixj > i) {
+          bool up = (i & k) == 0;
+          double a = sv[i], b = sv[ixj];
+          if ((a > b) == up) { sv[i] = b; sv[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  const int m = N - n_nan;
+  double med = __longlong_as_double(0x7ff8000000000000LL);
+  if (m > 0) med = (m & 1) ? sv[m / 2] : 0.5 * (sv[m / 2 - 1] + sv[m / 2]);
+  for (int i = threadIdx.x; i < N; i += blockDim.x)
+    if (isnan(v[i])) v[i] = med;
+}
+
+inline dim3 grid_rc(int cols, int rows, int B, int bt = 128) { return dim3(ceil_div(cols, bt), rows, B); }
+
+}  // namespace
+
+int prep_vectors(const PanelView& pv, int B, int NP, const int* date_t, const int* sel, const int* nsel, const BatchVecs& v,
+                 cudaStream_t s) {
+  prep_vectors_kernel<<<B, 256, 0, s>>>(pv, NP, date_t, sel, nsel, v);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int build_x_factor(const PanelView& pv, int B, int NP, const int* date_t, const int* sel, const int* nsel, const BatchVecs& v,
+                   double* x, double* sgr, double* yv, cudaStream_t s) {
+  dim3 grid(NP / 32, NP / 32, B), block(32, 8);
+  build_x_factor_kernel<<<grid, block, 0, s>>>(pv, NP, date_t, sel, nsel, v, x, sgr, yv);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* lam, const double* w, const double* rf, double mu,
+                  double gam, double* x, double* sgr, double* yv, double* isl, double* sl, cudaStream_t s) {
+  build_x_dense_kernel<<<grid_rc(NP, NP, B), 128, 0, s>>>(n, NP, sigma_gam, lam, w, rf, mu, gam, x, sgr, yv, isl, sl);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
+                const BatchVecs& v, double* St, double* signal_t, cudaStream_t s) {
+  dim3 grid(ceil_div(P, 128), pv.lb + 2, B);
+  standardize_kernel<<<grid, 128, NP * sizeof(int), s>>>(pv, NP, P, ldP, date_t, sel, nsel, v, St, signal_t);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int copy2(int B, long n_elem, const double* src, double* d1, double* d2, cudaStream_t s) {
+  long n = (long)B * n_elem;
+  int blocks = (int)((n + 255) / 256 > 148 * 16 ? 148 * 16 : (n + 255) / 256);
+  copy2_kernel<<<blocks, 256, 0, s>>>(n, src, d1, d2);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int add_mat(int B, long n_elem, const double* a, const double* b, double* out, cudaStream_t s) {
+  long n = (long)B * n_elem;
+  int blocks = (int)((n + 255) / 256 > 148 * 16 ? 148 * 16 : (n + 255) / 256);
+  add_kernel<<<blocks, 256, 0, s>>>(n, a, b, out);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int db_norms(int B, int NP, const double* M, const double* Mi, double* part, double* sc, cudaStream_t s) {
+  db_norms_partial_kernel<<<dim3(NORM_CHUNKS, B), 256, 0, s>>>(NP, M, Mi, part);
+  PFML_CHECK_LAUNCH();
+  db_norms_final_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, part, sc);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int db_update_M(int B, int NP, double* M, const double* Mi, double* Wk, const double* sc, cudaStream_t s) {
+  db_update_M_kernel<<<grid_rc(NP, NP, B), 128, 0, s>>>(NP, M, Mi, Wk, sc);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int mt0_from_sqrt(int B, int NP, const double* x, const double* Y, double* mt, cudaStream_t s) {
+  mt0_kernel<<<grid_rc(NP, NP, B), 128, 0, s>>>(NP, x, Y, mt);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int fp_build(int B, int NP, const double* x, const double* yv, const double* mt, const double* sgr, double* Wk, cudaStream_t s) {
+  fp_build_kernel<<<grid_rc(NP, NP, B), 128, 0, s>>>(NP, x, yv, mt, sgr, Wk);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int chain_init(int B, int NP, const double* mt, const double* g1, long sg, double* Bt, double* CB, cudaStream_t s) {
+  chain_init_kernel<<<grid_rc(NP, NP, B), 128, 0, s>>>(NP, mt, g1, sg, Bt, CB);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int row_scale(int B, int rows, int cols, long ld, long stride, const double* in, const double* rsv, long srs, double* out,
+              long ldo, long stride_o, cudaStream_t s) {
+  row_scale_kernel<<<grid_rc(cols, rows, B), 128, 0, s>>>(rows, cols, ld, stride, in, rsv, srs, out, ldo, stride_o);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int m_from_mtilde(int B, int n, int NP, const double* mt, const double* isl, const double* sl, double* m_out, cudaStream_t s) {
+  m_from_mtilde_kernel<<<grid_rc(n, n, B), 128, 0, s>>>(n, NP, mt, isl, sl, m_out);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int base_inverse(int B, int NP, const double* src, double* dst, int off, int* status, cudaStream_t s) {
+  base_inverse_kernel<<<B, 256, 0, s>>>(NP, src, dst, off, status);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int gemv_t(int B, int rows, int cols, const double* A, long ld, long sA, const double* v, long sv, double* out, long so,
+           cudaStream_t s) {
+  gemv_t_kernel<<<dim3(ceil_div(cols, 128), B), 128, 0, s>>>(rows, cols, A, ld, sA, v, sv, out, so);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int gt_panel(long n, const double* tr_ld0, const double* mu_ld0, double* gt, cudaStream_t s) {
+  gt_kernel<<<ceil_div(n, 256), 256, 0, s>>>(n, tr_ld0, mu_ld0, gt);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int vol_scale_panel(const double* fct_load, const double* fct_cov, const double* ivol, const unsigned char* has, int T, int N,
+                    int K, double* vol_scale, cudaStream_t s) {
+  vol_scale_kernel<<<dim3(ceil_div(N, 128), T), 128, K * K * sizeof(double), s>>>(fct_load, fct_cov, ivol, has, N, K, vol_scale);
+  PFML_CHECK_LAUNCH();
+  if (has) {
+    int npow = 1;
+    while (npow < N) npow <<= 1;
+    if (npow > 4096 * 4) {
+      set_error("pfml_vol_scale: median fill supports N <= 16384 stocks per month (got %d)", N);
+      return -2;
+    }
+    size_t smem = (size_t)npow * sizeof(double);
+    static bool cfg[64] = {};
+    int dev = 0;
+    PFML_CUDA_OK(cudaGetDevice(&dev));
+    if (!cfg[dev & 63]) {
+      PFML_CUDA_OK(cudaFuncSetAttribute(median_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8));
+      cfg[dev & 63] = true;
+    }
+    median_fill_kernel<<<T, 512, smem, s>>>(N, npow, vol_scale);
+    PFML_CHECK_LAUNCH();
+  }
+  return 0;
+}
+
+int check_finite_status(int B, const double* sc, int* status, cudaStream_t s) {
+  check_status_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, sc, status);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace pfml

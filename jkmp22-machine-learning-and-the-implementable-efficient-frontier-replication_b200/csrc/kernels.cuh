@@ -1,0 +1,75 @@
+// Launchers of the non-GEMM kernels of the PFML date-step (kernels.cu).  Internal header.
+#pragma once
+#include "common.cuh"
+
+namespace pfml {
+
+// Device view of the resident panel (mirrors pfml_panel_t of include/pfml_b200.h).
+struct PanelView {
+  int T, N, F, p, K;
+  const double* rff;        // [T*N][p]  [cos | sin]
+  const double* vol_scale;  // [T*N]
+  const double* gt;         // [T*N]  (1+tr_ld0)/(1+mu_ld0), NaN where missing
+  const double* lam;        // [T*N]
+  const double* ret_ld1;    // [T*N]
+  const double* fct_load;   // [T*N][K]
+  const double* fct_cov;    // [T][K][K]
+  const double* ivol;       // [T*N]
+  const double* wealth;     // [T]
+  const double* rf;         // [T]
+  double gamma_rel, mu;
+  int lb, iterations;
+};
+
+constexpr int KP = 32;         // factor count padded (K <= 32)
+constexpr int BASE = 64;       // base block of the recursive inversion
+constexpr int NSCAL = 8;       // per-date scalars: 0 gamma/w... see prep_vectors
+constexpr int NORM_CHUNKS = 16;
+
+struct BatchVecs {             // per-date vectors, all [B][NP] unless noted
+  double* sl;      // sqrt(lambda)            (pad 1)
+  double* isl;     // lambda^-1/2             (pad 1)
+  double* g;       // [B][lb+2][NP] g_tau with NaN->1 (pad 1)
+  double* g0raw;   // g_0 without NaN->1      (pad 1)
+  double* rv;      // lambda^-1/2 * ret_ld1   (pad 0)
+  double* dvl;     // gamma * ivol / lambda   (pad 0)
+  double* Lg;      // [B][NP][KP] gathered factor loadings (pad 0)
+  double* Lt;      // [B][NP][KP] lambda^-1/2 * L
+  double* LF;      // [B][NP][KP] L @ fct_cov
+  double* Fg;      // [B][KP][KP] gamma * fct_cov, zero padded
+  double* scal;    // [B][NSCAL]: 0: w, 1: 1/w, 2: 1+rf+mu, 3: gamma
+};
+
+int prep_vectors(const PanelView& pv, int B, int NP, const int* date_t, const int* sel, const int* nsel,
+                 const BatchVecs& v, cudaStream_t s);
+int build_x_factor(const PanelView& pv, int B, int NP, const int* date_t, const int* sel, const int* nsel,
+                   const BatchVecs& v, double* x, double* sgr, double* yv, cudaStream_t s);
+int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* lam, const double* w, const double* rf,
+                  double mu, double gam, double* x, double* sgr, double* yv, double* isl, double* sl, cudaStream_t s);
+
+int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
+                const BatchVecs& v, double* St /*[B][lb+2][NP][ldP]*/, double* signal_t /*[B][NP][P] or null*/, cudaStream_t s);
+
+// n x n helpers on [B][NP][NP] buffers
+int copy2(int B, long n_elem, const double* src, double* d1, double* d2, cudaStream_t s);
+int db_norms(int B, int NP, const double* M, const double* Mi, double* part, double* sc /*[B][8]*/, cudaStream_t s);
+int db_update_M(int B, int NP, double* M, const double* Mi, double* Wk, const double* sc, cudaStream_t s);
+int mt0_from_sqrt(int B, int NP, const double* x, const double* Y, double* mt, cudaStream_t s);
+int fp_build(int B, int NP, const double* x, const double* yv, const double* mt, const double* sgr, double* Wk, cudaStream_t s);
+int chain_init(int B, int NP, const double* mt, const double* g1, long sg, double* Bt, double* CB, cudaStream_t s);
+int add_mat(int B, long n_elem, const double* a, const double* b, double* out, cudaStream_t s);
+int row_scale(int B, int rows, int cols, long ld, long stride, const double* in, const double* rsv, long srs, double* out,
+              long ldo, long stride_o, cudaStream_t s);
+int m_from_mtilde(int B, int n, int NP, const double* mt, const double* isl, const double* sl, double* m_out, cudaStream_t s);
+
+int base_inverse(int B, int NP, const double* src, double* dst, int off, int* status, cudaStream_t s);
+int gemv_t(int B, int rows, int cols, const double* A, long ld, long sA, const double* v, long sv, double* out, long so,
+           cudaStream_t s);
+int check_finite_status(int B, const double* sc, int* status, cudaStream_t s);
+
+// panel-level helpers
+int gt_panel(long n, const double* tr_ld0, const double* mu_ld0, double* gt, cudaStream_t s);
+int vol_scale_panel(const double* fct_load, const double* fct_cov, const double* ivol, const unsigned char* has, int T, int N,
+                    int K, double* vol_scale, cudaStream_t s);
+
+}  // namespace pfml

@@ -1,0 +1,613 @@
+// Orchestration of the PFML date-step on one B200 and the C ABI (include/pfml_b200.h).
+//
+// Mathematical restatement used on the device (every identity is exact; only rounding order differs from the
+// reference, checked against the oracle at <= 1e-8 relative, typically 1e-13):
+//   * Lambda is a vector (quirk Q11); everything runs in the "tilde" domain  m = L^-1/2 m~ L^1/2,
+//     omega = L^-1/2 omega~  (L = diag(lambda)), so the symmetric, well-conditioned m~ is the GEMM operand.
+//   * sqrtm(sigma_hat^2 - 4I) (General_functions.py:956) = sqrt(x^2 + 4x): scaled product-form
+//     Denman-Beavers iteration, GEMM + block inverse only.
+//   * inv() (General_functions.py:960) and the two solves (PFML_Input_Data.py:455-456): recursive
+//     Schur-complement block inverse, 64x64 Gauss-Jordan base blocks, everything else DMMA GEMMs.
+//   * chains (PFML_Input_Data.py:419-453): shared prefix A_{theta+1} = (m G_0) B_theta and Horner's rule,
+//     11 n^3 + 12 n^2 P GEMMs instead of 22 + 24.
+//   * risk = gamma omega' Sigma omega from the factor form Sigma = L F L' + diag(ivol) as one stacked
+//     (n+K)-deep contraction; tc = w omega_chg' Lambda omega_chg = w omega~_chg' omega~_chg; both symmetric
+//     (lower tiles computed, mirrored), denom = risk + tc fused in the tc epilogue.
+#include <cstdarg>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "kernels.cuh"
+#include "pfml_b200.h"
+
+namespace pfml {
+
+// ------------------------------------------------------------------------------------------------
+// errors, launch counter, profiling
+// ------------------------------------------------------------------------------------------------
+long g_launch_count = 0;
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+static const char* kTagNames[] = {"dmma_gemm", "standardize", "m_func", "chain_nxn", "horner_nxP", "solve", "denom",
+                                  "rff", "ridge", "cov", "other"};
+constexpr int N_TAGS = 11;   // slot 0 = all GEMM launches (tag -1), slots 1.. = ProfTag + ... see slot_of
+static int slot_of(int tag) {
+  switch (tag) {
+    case -1: return 0;
+    case T_STD: return 1;
+    case T_MFUNC: return 2;
+    case T_CHAIN: return 3;
+    case T_HORNER: return 4;
+    case T_SOLVE: return 5;
+    case T_DENOM: return 6;
+    case T_RFF: return 7;
+    case T_RIDGE: return 8;
+    case T_COV: return 9;
+    default: return 10;
+  }
+}
+struct ProfRec { int slot; cudaEvent_t e0, e1; double flops; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_recs;
+static std::vector<cudaEvent_t> g_open[N_TAGS];
+static std::mutex g_prof_mu;
+
+void prof_begin(int tag, cudaStream_t s) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  cudaEventRecord(e, s);
+  g_open[slot_of(tag)].push_back(e);
+}
+void prof_end(int tag, cudaStream_t s, double flops, double) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  int sl = slot_of(tag);
+  if (g_open[sl].empty()) return;
+  cudaEvent_t e0 = g_open[sl].back();
+  g_open[sl].pop_back();
+  cudaEvent_t e1;
+  cudaEventCreate(&e1);
+  cudaEventRecord(e1, s);
+  g_recs.push_back({sl, e0, e1, flops});
+}
+
+// ------------------------------------------------------------------------------------------------
+// workspace carving
+// ------------------------------------------------------------------------------------------------
+struct Carver {
+  char* base; size_t off = 0, cap;
+  Carver(void* p, size_t c) : base((char*)p), cap(c) {}
+  template <class T> T* take(size_t n) {
+    size_t bytes = (n * sizeof(T) + 255) / 256 * 256;
+    T* r = base ? (T*)(base + off) : nullptr;
+    off += bytes;
+    return r;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// recursive block inverse (np.linalg.inv, General_functions.py:960; np.linalg.solve, PFML_Input_Data.py:455)
+//   M = [A B; C D],  S = D - C A^-1 B,
+//   M^-1 = [A^-1 + W S^-1 V, -W S^-1; -S^-1 V, S^-1],  W = A^-1 B, V = C A^-1.
+// Wk (destroyed) holds M, X receives M^-1, T1 holds W and V.  All [B][NP][NP].
+// ------------------------------------------------------------------------------------------------
+struct InvCtx { int B, NP; double *Wk, *X, *T1; int* status; cudaStream_t s; };
+
+static int inv_rec(const InvCtx& c, int off, int size) {
+  if (size <= BASE) return base_inverse(c.B, c.NP, c.Wk, c.X, off, c.status, c.s);
+  const int nb = size / BASE, h = ((nb + 1) / 2) * BASE, r = size - h;
+  const long NP = c.NP, NN = NP * NP;
+  auto at = [&](double* base, int r0, int c0) { return base + (long)r0 * NP + c0; };
+  PFML_TRY(inv_rec(c, off, h));
+  GemmP g;
+  g.lda = g.ldb = g.ldd = g.lde = NP;
+  g.sA = g.sB = g.sD = g.sE = NN;
+  // W = X11 * B
+  g.A = at(c.X, off, off); g.B = at(c.Wk, off, off + h); g.D = at(c.T1, off, off + h);
+  g.M = h; g.N = r; g.K = h;
+  PFML_TRY(gemm(g, c.B, c.s));
+  // V = C * X11
+  g.A = at(c.Wk, off + h, off); g.B = at(c.X, off, off); g.D = at(c.T1, off + h, off);
+  g.M = r; g.N = h; g.K = h;
+  PFML_TRY(gemm(g, c.B, c.s));
+  // S = D - C * W   (in place over D)
+  g.A = at(c.Wk, off + h, off); g.B = at(c.T1, off, off + h); g.D = at(c.Wk, off + h, off + h);
+  g.E = g.D; g.alpha = -1.0; g.beta = 1.0;
+  g.M = r; g.N = r; g.K = h;
+  PFML_TRY(gemm(g, c.B, c.s));
+  PFML_TRY(inv_rec(c, off + h, r));
+  // X12 = -W * X22
+  g.E = nullptr; g.beta = 0.0;
+  g.A = at(c.T1, off, off + h); g.B = at(c.X, off + h, off + h); g.D = at(c.X, off, off + h);
+  g.M = h; g.N = r; g.K = r;
+  PFML_TRY(gemm(g, c.B, c.s));
+  // X21 = -X22 * V
+  g.A = at(c.X, off + h, off + h); g.B = at(c.T1, off + h, off); g.D = at(c.X, off + h, off);
+  g.M = r; g.N = h; g.K = r;
+  PFML_TRY(gemm(g, c.B, c.s));
+  // X11 = X11 - X12 * V
+  g.A = at(c.X, off, off + h); g.B = at(c.T1, off + h, off); g.D = at(c.X, off, off);
+  g.E = g.D; g.beta = 1.0;
+  g.M = h; g.N = h; g.K = r;
+  PFML_TRY(gemm(g, c.B, c.s));
+  return 0;
+}
+
+static int inverse(const InvCtx& c) { return inv_rec(c, 0, c.NP); }
+
+// ------------------------------------------------------------------------------------------------
+// m_tilde: General_functions.py:955-960 given x, sigma_gr, y.  Result pointer returned in *mt_out
+// (one of mt / Xinv, they ping-pong).
+// ------------------------------------------------------------------------------------------------
+constexpr int DB_ITERS = 10;
+
+struct MtBufs {
+  double *x, *sgr, *yv, *Mdb, *Wk, *Xinv, *T1, *Ya, *Yb, *mt, *part, *sc;
+};
+
+static int mtilde(int B, int NP, int iterations, const MtBufs& m, int* status, cudaStream_t s, double** mt_out) {
+  const long NN = (long)NP * NP;
+  GemmP g;
+  g.lda = g.ldb = g.ldd = g.lde = NP;
+  g.sA = g.sB = g.sD = g.sE = NN;
+  g.M = g.N = g.K = NP;
+  // A = sigma_hat^2 - 4I = x^2 + 4x   (symmetric)
+  g.A = m.x; g.B = m.x; g.E = m.x; g.beta = 4.0; g.D = m.Mdb; g.sym = 1;
+  PFML_TRY(gemm(g, B, s));
+  PFML_TRY(copy2(B, NN, m.Mdb, m.Ya, m.Wk, s));
+  double *Ya = m.Ya, *Yb = m.Yb;
+  InvCtx ic{B, NP, m.Wk, m.Xinv, m.T1, status, s};
+  for (int k = 0; k < DB_ITERS; k++) {
+    PFML_TRY(inverse(ic));
+    PFML_TRY(db_norms(B, NP, m.Mdb, m.Xinv, m.part, m.sc, s));
+    // Y <- 0.5 mu Y + (0.5/mu) Y M^-1
+    GemmP y;
+    y.lda = y.ldb = y.ldd = y.lde = NP;
+    y.sA = y.sB = y.sD = y.sE = NN;
+    y.M = y.N = y.K = NP;
+    y.A = Ya; y.B = m.Xinv; y.E = Ya; y.D = Yb;
+    y.alpha = 1.0; y.beta = 1.0; y.az = m.sc + 0; y.bz = m.sc + 1; y.s_z = 8;
+    PFML_TRY(gemm(y, B, s));
+    // M <- 0.5 (I + 0.5 (mu^2 M + M^-1 / mu^2)),  copy into Wk for the next inverse
+    PFML_TRY(db_update_M(B, NP, m.Mdb, m.Xinv, m.Wk, m.sc, s));
+    double* t = Ya; Ya = Yb; Yb = t;
+  }
+  if (status) PFML_TRY(check_finite_status(B, m.sc, status, s));
+  double *mt = m.mt, *other = m.Xinv;
+  PFML_TRY(mt0_from_sqrt(B, NP, m.x, Ya, mt, s));
+  for (int it = 0; it < iterations; it++) {
+    PFML_TRY(fp_build(B, NP, m.x, m.yv, mt, m.sgr, m.Wk, s));
+    InvCtx fc{B, NP, m.Wk, other, m.T1, status, s};
+    PFML_TRY(inverse(fc));
+    double* t = mt; mt = other; other = t;
+  }
+  *mt_out = mt;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// date-step workspace
+// ------------------------------------------------------------------------------------------------
+struct StepWs {
+  int B, NP, P, nt; long ldP;
+  BatchVecs v;
+  MtBufs m;
+  double *XC, *XCl1;
+  double *St, *Za, *Zb, *Nn, *Nl1, *OM, *BS, *OMC;
+  double *risk_tmp, *tc_tmp;
+  size_t bytes;
+};
+
+static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, bool need_risk, bool need_tc) {
+  StepWs w{};
+  w.B = B; w.NP = NP; w.P = P; w.nt = nt;
+  w.ldP = round_up(P, 8);
+  Carver c(ws, cap);
+  const size_t NN = (size_t)NP * NP, BNN = B * NN, nP = (size_t)NP * w.ldP, BnP = B * nP;
+  w.v.sl = c.take<double>((size_t)B * NP);
+  w.v.isl = c.take<double>((size_t)B * NP);
+  w.v.g = c.take<double>((size_t)B * nt * NP);
+  w.v.g0raw = c.take<double>((size_t)B * NP);
+  w.v.rv = c.take<double>((size_t)B * NP);
+  w.v.dvl = c.take<double>((size_t)B * NP);
+  w.v.Lg = c.take<double>((size_t)B * NP * KP);
+  w.v.Lt = c.take<double>((size_t)B * NP * KP);
+  w.v.LF = c.take<double>((size_t)B * NP * KP);
+  w.v.Fg = c.take<double>((size_t)B * KP * KP);
+  w.v.scal = c.take<double>((size_t)B * NSCAL);
+  w.m.x = c.take<double>(BNN); w.m.sgr = c.take<double>(BNN); w.m.yv = c.take<double>((size_t)B * NP);
+  w.m.Mdb = c.take<double>(BNN); w.m.Wk = c.take<double>(BNN); w.m.Xinv = c.take<double>(BNN);
+  w.m.T1 = c.take<double>(BNN); w.m.Ya = c.take<double>(BNN); w.m.Yb = c.take<double>(BNN);
+  w.m.mt = c.take<double>(BNN);
+  w.m.part = c.take<double>((size_t)B * NORM_CHUNKS * 3);
+  w.m.sc = c.take<double>((size_t)B * 8);
+  w.XC = c.take<double>(BNN); w.XCl1 = c.take<double>(BNN);
+  w.St = c.take<double>((size_t)nt * BnP);
+  w.Za = c.take<double>(BnP); w.Zb = c.take<double>(BnP);
+  w.Nn = c.take<double>(BnP); w.Nl1 = c.take<double>(BnP);
+  w.OM = c.take<double>((size_t)B * (NP + KP) * w.ldP);
+  w.BS = c.take<double>((size_t)B * (NP + KP) * w.ldP);
+  w.OMC = c.take<double>(BnP);
+  w.risk_tmp = need_risk ? c.take<double>((size_t)B * P * P) : nullptr;
+  w.tc_tmp = need_tc ? c.take<double>((size_t)B * P * P) : nullptr;
+  w.bytes = c.off;
+  return w;
+}
+
+static PanelView view_of(const pfml_panel_t* p) {
+  PanelView v;
+  v.T = p->T; v.N = p->N; v.F = p->F; v.p = p->p; v.K = p->K;
+  v.rff = p->rff; v.vol_scale = p->vol_scale; v.gt = p->gt; v.lam = p->lam; v.ret_ld1 = p->ret_ld1;
+  v.fct_load = p->fct_load; v.fct_cov = p->fct_cov; v.ivol = p->ivol; v.wealth = p->wealth; v.rf = p->rf;
+  v.gamma_rel = p->gamma_rel; v.mu = p->mu; v.lb = p->lb; v.iterations = p->iterations;
+  return v;
+}
+
+static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                           double* r_tilde, double* denom, double* risk, double* tc, double* signal_t, int* status,
+                           void* workspace, size_t workspace_bytes, cudaStream_t s) {
+  if (!panel || B <= 0 || n_max <= 0 || !date_t || !sel || !n_sel || !r_tilde || !denom || !workspace) {
+    set_error("pfml_date_steps: null/empty argument");
+    return -1;
+  }
+  if (panel->K > KP || panel->K <= 0) {
+    set_error("pfml_date_steps: K = %d factors unsupported (1..%d)", panel->K, KP);
+    return -2;
+  }
+  if (panel->lb < 2 || panel->p < 2 || (panel->p & 1)) {
+    set_error("pfml_date_steps: need lb >= 2 and even p >= 2 (lb=%d p=%d)", panel->lb, panel->p);
+    return -2;
+  }
+  const PanelView pv = view_of(panel);
+  const int NP = pfml_padded_n(n_max), P = pv.p + 1, nt = pv.lb + 2, lb = pv.lb;
+  StepWs w = carve_step(workspace, workspace_bytes, B, NP, P, nt, risk == nullptr, tc == nullptr);
+  if (w.bytes > workspace_bytes) {
+    set_error("pfml_date_steps: workspace too small (%zu < %zu bytes)", workspace_bytes, w.bytes);
+    return -3;
+  }
+  if (!risk) risk = w.risk_tmp;
+  if (!tc) tc = w.tc_tmp;
+  const long NN = (long)NP * NP, ldP = w.ldP, nP = (long)NP * ldP, sStack = (long)(NP + KP) * ldP;
+  if (status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
+
+  // ---- a3/a4 gathers + a6 standardise -----------------------------------------------------------
+  {
+    ProfScope ps(T_STD, s);
+    PFML_TRY(prep_vectors(pv, B, NP, date_t, sel, n_sel, w.v, s));
+    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, s));
+  }
+  auto St = [&](int tau) { return w.St + (long)tau * NP * ldP; };   // + b * nt * nP per batch
+  const long sSt = (long)nt * nP;
+  auto gv = [&](int tau) { return w.v.g + (long)tau * NP; };        // + b * nt * NP per batch
+  const long sg = (long)nt * NP;
+
+  // ---- a5 m_tilde -------------------------------------------------------------------------------
+  double* mt = nullptr;
+  {
+    ProfScope ps(T_MFUNC, s);
+    PFML_TRY(build_x_factor(pv, B, NP, date_t, sel, n_sel, w.v, w.m.x, w.m.sgr, w.m.yv, s));
+    PFML_TRY(mtilde(B, NP, pv.iterations, w.m, status, s, &mt));
+  }
+  // free n x n buffers after m_tilde: x, sgr, Mdb, Ya, Yb, Wk, T1 and whichever of {mt, Xinv} is not `mt`
+  double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
+  double* spare = (mt == w.m.mt) ? w.m.Xinv : w.m.mt;
+
+  // ---- a7 chain of n x n products (tilde domain) ------------------------------------------------
+  //   B~_1 = m~ G_1, B~_{k+1} = B~_k m~ G_{k+1};  CB = sum_{k=0}^{lb-1} B~_k;  B11 = B~_lb
+  {
+    ProfScope ps(T_CHAIN, s);
+    PFML_TRY(chain_init(B, NP, mt, gv(1), sg, Bt_a, CB, s));
+    GemmP g;
+    g.lda = g.ldb = g.ldd = NP; g.sA = g.sB = g.sD = NN;
+    g.M = g.N = g.K = NP;
+    for (int k = 1; k < lb; k++) {
+      const bool last = (k == lb - 1);
+      g.A = Bt_a; g.B = mt; g.D = last ? B11 : Bt_b;
+      g.cs = gv(k + 1); g.s_cs = sg;
+      g.D2 = last ? nullptr : CB; g.E2 = last ? nullptr : CB;
+      PFML_TRY(gemm(g, B, s));
+      double* t = Bt_a; Bt_a = Bt_b; Bt_b = t;
+    }
+    // const_l1~ = CB + B11 -> Wk (to be inverted);  const~ = I + m~ (G_0 CB) -> spare (to be inverted)
+    PFML_TRY(add_mat(B, NN, CB, B11, w.m.Wk, s));
+    PFML_TRY(row_scale(B, NP, NP, NP, NN, CB, gv(0), sg, CBs, NP, NN, s));
+    GemmP c;
+    c.lda = c.ldb = c.ldd = NP; c.sA = c.sB = c.sD = NN;
+    c.M = c.N = c.K = NP;
+    c.A = mt; c.B = CBs; c.D = spare; c.diag = 1.0;
+    PFML_TRY(gemm(c, B, s));
+  }
+
+  // ---- a8 Horner accumulation of the n x P sums -------------------------------------------------
+  //   Z'_j = G_j (S~_{j+1} + m~ Z'_{j+1}),  Z'_{lb-1} = G_{lb-1} S~_lb ;  Z = S~_1 + m~ Z'_1
+  //   N = S~_0 + m~ G_0 Z ;  N_l1 = Z + B11 S~_{lb+1}
+  double* Z = nullptr;
+  {
+    ProfScope ps(T_HORNER, s);
+    GemmP g;
+    g.lda = NP; g.sA = NN; g.ldb = ldP; g.ldd = ldP; g.lde = ldP; g.sE = sSt;
+    g.M = NP; g.N = P; g.K = NP;
+    g.A = mt; g.beta = 1.0;
+    const double* Zp = St(lb);         // already scaled by g_{lb-1} in the standardise kernel
+    long sZp = sSt;
+    double *za = w.Za, *zb = w.Zb;
+    for (int j = lb - 2; j >= 0; j--) {
+      g.B = Zp; g.sB = sZp; g.D = za; g.sD = nP;
+      g.E = St(j + 1);
+      g.rs = (j >= 1) ? gv(j) : nullptr; g.s_rs = sg;
+      PFML_TRY(gemm(g, B, s));
+      Zp = za; sZp = nP;
+      double* t = za; za = zb; zb = t;
+    }
+    Z = (double*)Zp;                    // unscaled Z (j = 0 step)
+    double* ZG = za;                    // the other ping-pong buffer
+    PFML_TRY(row_scale(B, NP, P, ldP, nP, Z, gv(0), sg, ZG, ldP, nP, s));
+    g.rs = nullptr;
+    g.B = ZG; g.sB = nP; g.D = w.Nn; g.sD = nP; g.E = St(0); g.sE = sSt;
+    PFML_TRY(gemm(g, B, s));
+    g.A = B11; g.B = St(lb + 1); g.sB = sSt; g.D = w.Nl1; g.E = Z; g.sE = nP;
+    PFML_TRY(gemm(g, B, s));
+  }
+
+  // ---- a8 solves: omega~ = const~^-1 N, omega~_l1 = const~_l1^-1 N_l1, omega~_chg -----------------
+  {
+    ProfScope ps(T_SOLVE, s);
+    // const~ sits in `spare`; move it to Wk after const_l1 has been inverted
+    InvCtx i1{B, NP, w.m.Wk, w.XCl1, w.m.T1, status, s};
+    PFML_TRY(inverse(i1));
+    InvCtx i0{B, NP, spare, w.XC, w.m.T1, status, s};
+    PFML_TRY(inverse(i0));
+    GemmP g;
+    g.lda = NP; g.sA = NN; g.ldb = ldP; g.sB = nP; g.ldd = ldP;
+    g.M = NP; g.N = P; g.K = NP;
+    g.A = w.XC; g.B = w.Nn; g.D = w.OM; g.sD = sStack;
+    PFML_TRY(gemm(g, B, s));
+    // omega~_chg = omega~ - g0raw o (const_l1^-1 N_l1)   (quirk Q8: g0 without NaN->1)
+    g.A = w.XCl1; g.B = w.Nl1; g.D = w.OMC; g.sD = nP;
+    g.alpha = -1.0; g.rs = w.v.g0raw; g.s_rs = NP;
+    g.E = w.OM; g.lde = ldP; g.sE = sStack; g.beta = 1.0;
+    PFML_TRY(gemm(g, B, s));
+  }
+
+  // ---- a9 r_tilde, risk, tc, denom ----------------------------------------------------------------
+  {
+    ProfScope ps(T_DENOM, s);
+    PFML_TRY(gemv_t(B, NP, P, w.OM, ldP, sStack, w.v.rv, NP, r_tilde, P, s));
+    // Y = (L^-1/2 Lf)' omega~  -> rows NP.. of the OM stack
+    GemmP y;
+    y.a_kinner = false; y.A = w.v.Lt; y.lda = KP; y.sA = (long)NP * KP;
+    y.B = w.OM; y.ldb = ldP; y.sB = sStack;
+    y.D = w.OM + (long)NP * ldP; y.ldd = ldP; y.sD = sStack;
+    y.M = KP; y.N = P; y.K = NP;
+    PFML_TRY(gemm(y, B, s));
+    // gamma F Y -> rows NP.. of the BS stack;  gamma (ivol/lambda) o omega~ -> rows 0..NP-1
+    GemmP f;
+    f.A = w.v.Fg; f.lda = KP; f.sA = KP * KP;
+    f.B = w.OM + (long)NP * ldP; f.ldb = ldP; f.sB = sStack;
+    f.D = w.BS + (long)NP * ldP; f.ldd = ldP; f.sD = sStack;
+    f.M = KP; f.N = P; f.K = KP;
+    PFML_TRY(gemm(f, B, s));
+    PFML_TRY(row_scale(B, NP, P, ldP, sStack, w.OM, w.v.dvl, NP, w.BS, ldP, sStack, s));
+    // risk = [omega~; Y]' [gamma (ivol/lambda) omega~; gamma F Y]
+    GemmP r;
+    r.a_kinner = false; r.A = w.OM; r.lda = ldP; r.sA = sStack;
+    r.B = w.BS; r.ldb = ldP; r.sB = sStack;
+    r.D = risk; r.ldd = P; r.sD = (long)P * P;
+    r.M = P; r.N = P; r.K = NP + KP; r.sym = 1;
+    PFML_TRY(gemm(r, B, s));
+    // tc = w omega~_chg' omega~_chg ; denom = risk + tc
+    GemmP t;
+    t.a_kinner = false; t.A = w.OMC; t.lda = ldP; t.sA = nP;
+    t.B = w.OMC; t.ldb = ldP; t.sB = nP;
+    t.D = tc; t.ldd = P; t.sD = (long)P * P;
+    t.D2 = denom; t.E2 = risk;
+    t.az = w.v.scal + 0; t.s_z = NSCAL;
+    t.M = P; t.N = P; t.K = NP; t.sym = 1;
+    PFML_TRY(gemm(t, B, s));
+  }
+  return 0;
+}
+
+}  // namespace pfml
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+using namespace pfml;
+
+extern "C" {
+
+const char* pfml_version(void) { return "pfml_b200 0.1 (sm_100a, FP64 DMMA)"; }
+const char* pfml_last_error(void) { return last_error(); }
+
+int pfml_padded_n(int n_max) { return (int)round_up(n_max < 1 ? 1 : n_max, BASE); }
+
+size_t pfml_date_steps_workspace_bytes(const pfml_panel_t* panel, int B, int n_max) {
+  if (!panel || B <= 0 || n_max <= 0) return 0;
+  StepWs w = carve_step(nullptr, 0, B, pfml_padded_n(n_max), panel->p + 1, panel->lb + 2, true, true);
+  return w.bytes;
+}
+
+int pfml_date_steps(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                    double* r_tilde, double* denom, double* risk, double* tc, double* signal_t, int* status,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+  return date_steps_impl(panel, B, n_max, date_t, sel, n_sel, r_tilde, denom, risk, tc, signal_t, status, workspace,
+                         workspace_bytes, (cudaStream_t)stream);
+}
+
+// ---- m_func ----------------------------------------------------------------------------------------
+static MtBufs carve_mt(Carver& c, int B, int NP, double** isl, double** sl) {
+  MtBufs m{};
+  const size_t BNN = (size_t)B * NP * NP;
+  m.x = c.take<double>(BNN); m.sgr = c.take<double>(BNN); m.yv = c.take<double>((size_t)B * NP);
+  m.Mdb = c.take<double>(BNN); m.Wk = c.take<double>(BNN); m.Xinv = c.take<double>(BNN);
+  m.T1 = c.take<double>(BNN); m.Ya = c.take<double>(BNN); m.Yb = c.take<double>(BNN); m.mt = c.take<double>(BNN);
+  m.part = c.take<double>((size_t)B * NORM_CHUNKS * 3);
+  m.sc = c.take<double>((size_t)B * 8);
+  *isl = c.take<double>((size_t)B * NP);
+  *sl = c.take<double>((size_t)B * NP);
+  return m;
+}
+
+size_t pfml_mfunc_workspace_bytes(int B, int n) {
+  if (B <= 0 || n <= 0) return 0;
+  Carver c(nullptr, 0);
+  double *a, *b;
+  carve_mt(c, B, pfml_padded_n(n), &a, &b);
+  return c.off;
+}
+
+int pfml_mfunc_batched(int B, int n, const double* sigma_gam, const double* lam, const double* w, const double* rf, double mu,
+                       double gam, int iterations, double* m_out, int* status, void* workspace, size_t workspace_bytes,
+                       void* stream) {
+  if (B <= 0 || n <= 0 || !sigma_gam || !lam || !w || !rf || !m_out || !workspace || iterations < 0) {
+    set_error("pfml_mfunc_batched: null/empty argument");
+    return -1;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const int NP = pfml_padded_n(n);
+  Carver c(workspace, workspace_bytes);
+  double *isl, *sl;
+  MtBufs m = carve_mt(c, B, NP, &isl, &sl);
+  if (c.off > workspace_bytes) {
+    set_error("pfml_mfunc_batched: workspace too small (%zu < %zu bytes)", workspace_bytes, c.off);
+    return -3;
+  }
+  if (status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
+  ProfScope ps(T_MFUNC, s);
+  PFML_TRY(build_x_dense(B, n, NP, sigma_gam, lam, w, rf, mu, gam, m.x, m.sgr, m.yv, isl, sl, s));
+  double* mt = nullptr;
+  PFML_TRY(mtilde(B, NP, iterations, m, status, s, &mt));
+  PFML_TRY(m_from_mtilde(B, n, NP, mt, isl, sl, m_out, s));
+  return 0;
+}
+
+// ---- generic GEMM / inverse --------------------------------------------------------------------------
+int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alpha, const double* A, long lda, long sA,
+                       const double* B, long ldb, long sB, double beta, double* D, long ldd, long sD, int batch, void* stream) {
+  GemmP g;
+  g.A = A; g.lda = lda; g.sA = sA; g.B = B; g.ldb = ldb; g.sB = sB; g.D = D; g.ldd = ldd; g.sD = sD;
+  g.M = M; g.N = N; g.K = K; g.alpha = alpha;
+  g.a_kinner = !trans_a; g.b_kinner = trans_b != 0;
+  if (beta != 0.0) { g.E = D; g.lde = ldd; g.sE = sD; g.beta = beta; }
+  return gemm(g, batch, (cudaStream_t)stream);
+}
+
+namespace {
+__global__ void pad_identity_kernel(int n, int NP, const double* __restrict__ A, double* __restrict__ Wk) {
+  const int b = blockIdx.z, r = blockIdx.y, c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= NP) return;
+  Wk[((long)b * NP + r) * NP + c] = (r < n && c < n) ? A[((long)b * n + r) * n + c] : (r == c ? 1.0 : 0.0);
+}
+__global__ void unpad_kernel(int n, int NP, const double* __restrict__ X, double* __restrict__ out) {
+  const int b = blockIdx.z, r = blockIdx.y, c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  out[((long)b * n + r) * n + c] = X[((long)b * NP + r) * NP + c];
+}
+}  // namespace
+
+size_t pfml_inverse_workspace_bytes(int B, int n) {
+  if (B <= 0 || n <= 0) return 0;
+  const size_t NP = pfml_padded_n(n);
+  return 3 * (((size_t)B * NP * NP * sizeof(double) + 255) / 256 * 256);
+}
+
+int pfml_inverse_batched(int B, int n, const double* A, double* Ainv, int* status, void* workspace, size_t workspace_bytes,
+                         void* stream) {
+  if (B <= 0 || n <= 0 || !A || !Ainv || !workspace) {
+    set_error("pfml_inverse_batched: null/empty argument");
+    return -1;
+  }
+  if (workspace_bytes < pfml_inverse_workspace_bytes(B, n)) {
+    set_error("pfml_inverse_batched: workspace too small");
+    return -3;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const int NP = pfml_padded_n(n);
+  Carver c(workspace, workspace_bytes);
+  const size_t BNN = (size_t)B * NP * NP;
+  double* Wk = c.take<double>(BNN);
+  double* X = c.take<double>(BNN);
+  double* T1 = c.take<double>(BNN);
+  if (status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
+  pad_identity_kernel<<<dim3(ceil_div(NP, 128), NP, B), 128, 0, s>>>(n, NP, A, Wk);
+  PFML_CHECK_LAUNCH();
+  InvCtx ic{B, NP, Wk, X, T1, status, s};
+  PFML_TRY(inverse(ic));
+  unpad_kernel<<<dim3(ceil_div(n, 128), n, B), 128, 0, s>>>(n, NP, X, Ainv);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---- a1 / a2 ----------------------------------------------------------------------------------------
+int pfml_rff_sincos(const double* X, const double* W, long rows, int F, int p_half, double* out, void* stream) {
+  if (!X || !W || !out || rows <= 0 || F <= 0 || p_half <= 0) {
+    set_error("pfml_rff_sincos: null/empty argument");
+    return -1;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  ProfScope ps(T_RFF, s);
+  const long chunk = 1L << 20;     // grid.y limit: 65535 row tiles
+  for (long r0 = 0; r0 < rows; r0 += chunk) {
+    GemmP g;
+    g.A = X + r0 * F; g.lda = F; g.B = W; g.ldb = p_half; g.D = out + r0 * 2L * p_half; g.ldd = 2L * p_half;
+    g.M = (int)((rows - r0) < chunk ? (rows - r0) : chunk); g.N = p_half; g.K = F;
+    g.sincos = 1;
+    PFML_TRY(gemm(g, 1, s));
+  }
+  return 0;
+}
+
+int pfml_growth_ratio(const double* tr_ld0, const double* mu_ld0, long n, double* gt, void* stream) {
+  if (!tr_ld0 || !mu_ld0 || !gt || n <= 0) {
+    set_error("pfml_growth_ratio: null/empty argument");
+    return -1;
+  }
+  return gt_panel(n, tr_ld0, mu_ld0, gt, (cudaStream_t)stream);
+}
+
+int pfml_vol_scale(const double* fct_load, const double* fct_cov, const double* ivol, const unsigned char* has, int T, int N,
+                   int K, double* vol_scale, void* stream) {
+  if (!fct_load || !fct_cov || !ivol || !vol_scale || T <= 0 || N <= 0 || K <= 0) {
+    set_error("pfml_vol_scale: null/empty argument");
+    return -1;
+  }
+  return vol_scale_panel(fct_load, fct_cov, ivol, has, T, N, K, vol_scale, (cudaStream_t)stream);
+}
+
+// ---- profiling ---------------------------------------------------------------------------------------
+void pfml_prof_enable(int on) { g_prof_on = on != 0; }
+int pfml_prof_ntags(void) { return N_TAGS; }
+const char* pfml_prof_tag_name(int tag) { return (tag >= 0 && tag < N_TAGS) ? kTagNames[tag] : "?"; }
+long pfml_launch_count(void) { return g_launch_count; }
+
+int pfml_prof_collect(double* ms, double* flops, double* launches) {
+  PFML_CUDA_OK(cudaDeviceSynchronize());
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (int i = 0; i < N_TAGS; i++) { ms[i] = 0; flops[i] = 0; launches[i] = 0; }
+  for (auto& r : g_recs) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, r.e0, r.e1);
+    ms[r.slot] += t; flops[r.slot] += r.flops; launches[r.slot] += 1;
+    cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+  }
+  g_recs.clear();
+  for (int i = 0; i < N_TAGS; i++) {
+    for (auto e : g_open[i]) cudaEventDestroy(e);
+    g_open[i].clear();
+  }
+  return 0;
+}
+
+}  // extern "C"

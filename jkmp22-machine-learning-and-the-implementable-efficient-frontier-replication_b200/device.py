@@ -1,0 +1,198 @@
+"""Device-side driver of the PFML date-steps: torch owns memory and streams, libpfml_b200.so does the math.
+
+``DevicePanel`` mirrors the panel-level part of PFML_Input_Data.py (rff :245-256, vol_scale :274-305) and
+``date_steps`` the per-date loop (:318-491).  Every arithmetic step is a call through the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import PanelStruct, check
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _dev(a, device, dtype=torch.float64):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(device)
+
+
+class DevicePanel:
+    """Panel resident in HBM: characteristics -> RFF features, Barra triples -> vol_scale, g_t, ...
+
+    Layout: dense [T*N] rows (month-major), FP64, row-major; see pfml_panel_t in include/pfml_b200.h.
+    """
+
+    def __init__(self, panel, device="cuda:0"):
+        lib = _lib.load()
+        self.device = torch.device(device)
+        self.host = panel
+        T, N, F = panel.feats.shape
+        K = panel.fct_cov.shape[1]
+        self.T, self.N, self.F, self.K, self.p = T, N, F, K, panel.p
+        with torch.cuda.device(self.device):
+            s = _stream_ptr()
+            feats = _dev(panel.feats.reshape(T * N, F), self.device)
+            W = _dev(panel.W, self.device)
+            self.W = W
+            self.rff = torch.empty((T * N, self.p), dtype=torch.float64, device=self.device)
+            check(lib.pfml_rff_sincos(_ptr(feats), _ptr(W), T * N, F, self.p // 2, _ptr(self.rff), s), "pfml_rff_sincos")
+            self.fct_load = _dev(panel.fct_load.reshape(T * N, K), self.device)
+            self.fct_cov = _dev(panel.fct_cov, self.device)
+            self.ivol = _dev(panel.ivol.reshape(-1), self.device)
+            has = _dev(panel.barra_has.reshape(-1).astype(np.uint8), self.device, torch.uint8)
+            self.vol_scale = torch.empty(T * N, dtype=torch.float64, device=self.device)
+            has_arg = _ptr(has) if not bool(panel.barra_has.all()) else C.c_void_p(0)
+            check(lib.pfml_vol_scale(_ptr(self.fct_load), _ptr(self.fct_cov), _ptr(self.ivol), has_arg, T, N, K,
+                                     _ptr(self.vol_scale), s), "pfml_vol_scale")
+            tr = _dev(panel.tr_ld0.reshape(-1), self.device)
+            mu = _dev(panel.mu_ld0.reshape(-1), self.device)
+            self.gt = torch.empty(T * N, dtype=torch.float64, device=self.device)
+            check(lib.pfml_growth_ratio(_ptr(tr), _ptr(mu), T * N, _ptr(self.gt), s), "pfml_growth_ratio")
+            self.lam = _dev(panel.lam.reshape(-1), self.device)
+            self.ret_ld1 = _dev(panel.ret_ld1.reshape(-1), self.device)
+            self.wealth = _dev(panel.wealth, self.device)
+            self.rf = _dev(panel.rf, self.device)
+            torch.cuda.current_stream().synchronize()
+        self.struct = PanelStruct(T=T, N=N, F=F, p=self.p, K=K, rff=self.rff.data_ptr(),
+                                  vol_scale=self.vol_scale.data_ptr(), gt=self.gt.data_ptr(), lam=self.lam.data_ptr(),
+                                  ret_ld1=self.ret_ld1.data_ptr(), fct_load=self.fct_load.data_ptr(),
+                                  fct_cov=self.fct_cov.data_ptr(), ivol=self.ivol.data_ptr(),
+                                  wealth=self.wealth.data_ptr(), rf=self.rf.data_ptr(),
+                                  gamma_rel=float(panel.gamma_rel), mu=float(panel.mu), lb=int(panel.lb),
+                                  iterations=int(panel.iterations))
+
+
+def universe(panel, months):
+    """Host-side index logic of PFML_Input_Data.py:321-327: the valid ids of each date, ascending."""
+    lib = _lib.load()
+    sels = [np.flatnonzero(panel.valid[t]).astype(np.int32) for t in months]
+    n_sel = np.array([len(s) for s in sels], dtype=np.int32)
+    n_max = int(n_sel.max())
+    NP = lib.pfml_padded_n(n_max)
+    sel = np.zeros((len(months), NP), dtype=np.int32)
+    for b, s in enumerate(sels):
+        sel[b, :len(s)] = s
+    return sel, n_sel, n_max, NP
+
+
+class DateStepRunner:
+    """Pre-allocated outputs + workspace for batches of B date-steps on one GPU."""
+
+    def __init__(self, dpanel: DevicePanel, B, n_max, want_risk_tc=True, want_signal=True):
+        lib = _lib.load()
+        self.dp = dpanel
+        self.B, self.n_max = B, n_max
+        self.NP = lib.pfml_padded_n(n_max)
+        P = dpanel.p + 1
+        self.P = P
+        dev = dpanel.device
+        f64 = dict(dtype=torch.float64, device=dev)
+        self.r_tilde = torch.empty((B, P), **f64)
+        self.denom = torch.empty((B, P, P), **f64)
+        self.risk = torch.empty((B, P, P), **f64) if want_risk_tc else None
+        self.tc = torch.empty((B, P, P), **f64) if want_risk_tc else None
+        self.signal_t = torch.empty((B, self.NP, P), **f64) if want_signal else None
+        self.status = torch.zeros(B, dtype=torch.int32, device=dev)
+        self.ws_bytes = lib.pfml_date_steps_workspace_bytes(C.byref(dpanel.struct), B, n_max)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
+        self.date_t = torch.empty(B, dtype=torch.int32, device=dev)
+        self.sel = torch.empty((B, self.NP), dtype=torch.int32, device=dev)
+        self.n_sel = torch.empty(B, dtype=torch.int32, device=dev)
+
+    def set_batch(self, months, sel, n_sel):
+        b = len(months)
+        assert b <= self.B and sel.shape[1] == self.NP
+        self.date_t[:b].copy_(torch.as_tensor(np.asarray(months, dtype=np.int32)))
+        self.sel[:b].copy_(torch.as_tensor(sel))
+        self.n_sel[:b].copy_(torch.as_tensor(n_sel))
+        self.b = b
+
+    def run(self):
+        lib = _lib.load()
+        with torch.cuda.device(self.dp.device):
+            check(lib.pfml_date_steps(C.byref(self.dp.struct), self.b, self.n_max, _ptr(self.date_t), _ptr(self.sel),
+                                      _ptr(self.n_sel), _ptr(self.r_tilde), _ptr(self.denom), _ptr(self.risk),
+                                      _ptr(self.tc), _ptr(self.signal_t), _ptr(self.status), _ptr(self.ws),
+                                      self.ws_bytes, _stream_ptr()), "pfml_date_steps")
+
+
+def date_steps(panel, months, device="cuda:0", dpanel=None):
+    """Run the date-steps of ``months`` (month indices into the panel) and return numpy outputs per date."""
+    months = list(months)
+    dpanel = dpanel or DevicePanel(panel, device)
+    sel, n_sel, n_max, NP = universe(panel, months)
+    runner = DateStepRunner(dpanel, len(months), n_max)
+    runner.set_batch(months, sel, n_sel)
+    runner.run()
+    torch.cuda.synchronize(dpanel.device)
+    status = runner.status.cpu().numpy()
+    out = []
+    for b, t in enumerate(months):
+        n = int(n_sel[b])
+        out.append(dict(r_tilde=runner.r_tilde[b].cpu().numpy(), denom=runner.denom[b].cpu().numpy(),
+                        risk=runner.risk[b].cpu().numpy(), tc=runner.tc[b].cpu().numpy(),
+                        signal_t=runner.signal_t[b, :n].cpu().numpy(), ids=panel.ids[sel[b, :n]], status=int(status[b])))
+    return out
+
+
+def m_func_batched(w, mu, rf, sigma_gam, gam, lam, iterations, device="cuda:0"):
+    """Batched m_func (General_functions.py:919-962): sigma_gam [B,n,n], lam [B,n] (diag of K_Lambda), w/rf [B]."""
+    lib = _lib.load()
+    dev = torch.device(device)
+    sg = _dev(sigma_gam, dev)
+    B, n, _ = sg.shape
+    lam_d, w_d, rf_d = _dev(lam, dev), _dev(np.broadcast_to(w, (B,)), dev), _dev(np.broadcast_to(rf, (B,)), dev)
+    out = torch.empty((B, n, n), dtype=torch.float64, device=dev)
+    status = torch.zeros(B, dtype=torch.int32, device=dev)
+    nbytes = lib.pfml_mfunc_workspace_bytes(B, n)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.pfml_mfunc_batched(B, n, _ptr(sg), _ptr(lam_d), _ptr(w_d), _ptr(rf_d), float(mu), float(gam),
+                                     int(iterations), _ptr(out), _ptr(status), _ptr(ws), nbytes, _stream_ptr()),
+              "pfml_mfunc_batched")
+        torch.cuda.synchronize(dev)
+    return out.cpu().numpy(), status.cpu().numpy()
+
+
+def dgemm(A, B, trans_a=False, trans_b=False, alpha=1.0, device="cuda:0"):
+    """D = alpha op(A) op(B) for [batch, ., .] arrays through pfml_dgemm_batched."""
+    lib = _lib.load()
+    dev = torch.device(device)
+    a, b = _dev(A, dev), _dev(B, dev)
+    batch = a.shape[0]
+    M = a.shape[2] if trans_a else a.shape[1]
+    K = a.shape[1] if trans_a else a.shape[2]
+    N = b.shape[1] if trans_b else b.shape[2]
+    d = torch.empty((batch, M, N), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.pfml_dgemm_batched(int(trans_a), int(trans_b), M, N, K, float(alpha), _ptr(a), a.shape[2],
+                                     a.shape[1] * a.shape[2], _ptr(b), b.shape[2], b.shape[1] * b.shape[2], 0.0, _ptr(d),
+                                     N, M * N, batch, _stream_ptr()), "pfml_dgemm_batched")
+        torch.cuda.synchronize(dev)
+    return d.cpu().numpy()
+
+
+def inverse(A, device="cuda:0"):
+    lib = _lib.load()
+    dev = torch.device(device)
+    a = _dev(A, dev)
+    B, n, _ = a.shape
+    out = torch.empty_like(a)
+    status = torch.zeros(B, dtype=torch.int32, device=dev)
+    nbytes = lib.pfml_inverse_workspace_bytes(B, n)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.pfml_inverse_batched(B, n, _ptr(a), _ptr(out), _ptr(status), _ptr(ws), nbytes, _stream_ptr()),
+              "pfml_inverse_batched")
+        torch.cuda.synchronize(dev)
+    return out.cpu().numpy(), status.cpu().numpy()

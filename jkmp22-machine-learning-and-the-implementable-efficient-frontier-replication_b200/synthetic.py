@@ -1,0 +1,155 @@
+"""Synthetic S&P-500-like panels for the PFML hot path (host code, numpy only).
+
+The reference ships no data (CRSP/JKP are proprietary), so every test, the oracle and
+``bench.py`` run on panels drawn here.  Value ranges follow SURVEY.md section 8(d) "C1..C5":
+characteristics are cross-sectional percentile ranks in [0, 1] (Prepare_Data.py:338-345,368),
+Kyle's lambda = 0.2 / dolvol (Prepare_Data.py:180), wealth is 1e10 at the end of the sample and
+back-cumulated (General_functions.py:205), and the Barra triple is
+(fct_load [one-hot FF12 | 13 z-scored cluster ranks], fct_cov, ivol_vec) as written by
+"Estimate Covariance Matrix.py":490-494.
+
+Everything is dense: month axis ``t`` (0 .. T_all-1, calendar month-ends), stock axis ``i``
+(ids ascending).  A ragged universe is expressed through ``valid[t, i]``; the
+reference needs a row for every id of date d in all 13 look-back months
+(PFML_Input_Data.py:357-361), which a dense panel gives by construction.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+
+N_FEATURES = 115          # len(get_features(True)), General_functions.py:113-170
+N_IND = 12                # FF12 one-hot industries
+N_CLUSTER = 13            # characteristic clusters
+LB = 11                   # pf_set['lb_hor'], General_functions.py:107
+
+
+@dataclass
+class Panel:
+    """Dense synthetic panel.  Shapes: T = months in panel, N = stocks, F = characteristics, K = factors."""
+    ids: np.ndarray            # [N] int64 ascending
+    month_ends: np.ndarray     # [T] datetime64[D] calendar month-ends
+    feats: np.ndarray          # [T, N, F] in [0, 1]
+    valid: np.ndarray          # [T, N] bool
+    ret_ld1: np.ndarray        # [T, N]
+    tr_ld0: np.ndarray         # [T, N]
+    mu_ld0: np.ndarray         # [T, N] (same value for every stock of a month)
+    lam: np.ndarray            # [T, N] Kyle's lambda
+    wealth: np.ndarray         # [T]
+    rf: np.ndarray             # [T] decimal monthly risk-free rate
+    fct_load: np.ndarray       # [T, N, K]
+    fct_cov: np.ndarray        # [T, K, K]
+    ivol: np.ndarray           # [T, N]
+    barra_has: np.ndarray      # [T, N] bool: id present in Barra_Cov[d]
+    W: np.ndarray              # [F, p/2] random-Fourier-feature frequencies (an INPUT, quirk Q1)
+    gamma_rel: float = 10.0
+    mu: float = 0.007
+    lb: int = LB
+    iterations: int = 10
+    meta: dict = field(default_factory=dict)
+
+    @property
+    def T(self):
+        return self.feats.shape[0]
+
+    @property
+    def N(self):
+        return self.feats.shape[1]
+
+    @property
+    def p(self):
+        return 2 * self.W.shape[1]
+
+    def hot_months(self):
+        """Month indices of dates_m2 (PFML_Input_Data.py:138-142): first_cov + lb+1 months .. last-1."""
+        return np.arange(self.lb + 1, self.T - 1)
+
+
+def month_end_range(start="2010-01", periods=24):
+    m = np.datetime64(start, "M") + np.arange(periods)
+    return (m + 1).astype("datetime64[D]") - np.timedelta64(1, "D")
+
+
+def make_panel(N=500, T=24, p=64, g=np.exp(-3.0), seed=1, F=N_FEATURES, ragged=0.0,
+               barra_missing=0.0, start="2010-01", nan_tr=0.0) -> Panel:
+    """Draw a panel.  ``ragged``: probability that a stock is invalid in a month (the universe then
+    differs by date); ``barra_missing``: probability that an id is absent from the Barra object of a
+    month (exercises the eom-median fill of vol_scale, PFML_Input_Data.py:300-305; only applied to
+    rows that are not in the date-d universe because create_cov(ids) needs them, General_functions.py:865);
+    ``nan_tr``: probability of a missing tr_ld0 in look-back months (quirk Q8)."""
+    rng = np.random.default_rng(seed)
+    K = N_IND + N_CLUSTER
+    ids = 10001 + np.arange(N, dtype=np.int64)
+    feats = rng.random((T, N, F))
+    valid = np.ones((T, N), dtype=bool)
+    if ragged > 0:
+        # a stock drops out for a stretch; validity needs all 13 look-back rows, which the dense panel has
+        valid = rng.random((T, N)) >= ragged
+    dolvol = np.exp(np.log(1e8) + rng.standard_normal(N))[None, :] * np.exp(0.1 * rng.standard_normal((T, N)))
+    lam = 0.2 / dolvol
+    tr = np.clip(0.01 + 0.08 * rng.standard_normal((T, N)), -0.9, None)
+    mu_m = 0.008 + 0.04 * rng.standard_normal(T)
+    mu_ld0 = np.repeat(mu_m[:, None], N, axis=1)
+    if nan_tr > 0:
+        mask = rng.random((T, N)) < nan_tr
+        tr = np.where(mask, np.nan, tr)
+    ret_ld1 = 0.006 + 0.08 * rng.standard_normal((T, N))
+    rf = rng.uniform(0.1, 0.4, T) / 100.0
+    # wealth: 1e10 at the end, back-cumulated with the market's total return (General_functions.py:205)
+    wealth = np.empty(T)
+    wealth[-1] = 1e10
+    for t in range(T - 2, -1, -1):
+        wealth[t] = wealth[t + 1] / (1.0 + mu_m[t + 1] + rf[t + 1])
+    # Barra triple
+    ind = rng.integers(0, N_IND, N)
+    onehot = np.zeros((N, N_IND))
+    onehot[np.arange(N), ind] = 1.0
+    fct_load = np.empty((T, N, K))
+    fct_cov = np.empty((T, K, K))
+    for t in range(T):
+        z = rng.standard_normal((N, N_CLUSTER))
+        z = (z - z.mean(0)) / z.std(0, ddof=1)
+        fct_load[t] = np.concatenate([onehot, z], axis=1)
+        A = rng.standard_normal((K, K))
+        fct_cov[t] = 21.0 * 0.005 ** 2 * (A @ A.T) / K
+    ivol = 21.0 * rng.uniform(0.008, 0.03, (T, N)) ** 2
+    barra_has = np.ones((T, N), dtype=bool)
+    if barra_missing > 0:
+        barra_has = rng.random((T, N)) >= barra_missing
+        barra_has |= valid          # create_cov(cov_list[d], ids) needs every universe id
+        # look-back rows of later universes may still be missing -> median fill path
+    W = np.sqrt(g) * rng.standard_normal((F, p // 2))
+    return Panel(ids=ids, month_ends=month_end_range(start, T), feats=feats, valid=valid, ret_ld1=ret_ld1,
+                 tr_ld0=tr, mu_ld0=mu_ld0, lam=lam, wealth=wealth, rf=rf, fct_load=fct_load, fct_cov=fct_cov,
+                 ivol=ivol, barra_has=barra_has, W=W, meta=dict(seed=seed, g=float(g)))
+
+
+def make_daily(N=60, years=12, seed=3, start="2008-01-01", F=N_FEATURES):
+    """Daily panel for the Barra/EWMA covariance estimator ("Estimate Covariance Matrix.py"), SURVEY C2.
+
+    Returns a dict of dense arrays: business days, per-(month, stock) characteristics + cluster map,
+    daily excess returns ret = X f + e with NaNs for missing observations."""
+    rng = np.random.default_rng(seed)
+    days = np.arange(np.datetime64(start, "D"), np.datetime64(start, "D") + np.timedelta64(int(366 * years), "D"))
+    dow = (days.astype("datetime64[D]").view("int64") - 4) % 7      # 1970-01-01 is a Thursday
+    days = days[(dow != 5) & (dow != 6)]                            # Monday=0 .. Friday=4 kept
+    months = np.unique(days.astype("datetime64[M]"))
+    Tm = len(months) + 1                                            # one extra lagged month in front
+    month_ends = ((np.concatenate([[months[0] - 1], months]) + 1).astype("datetime64[D]") - np.timedelta64(1, "D"))
+    ids = 10001 + np.arange(N, dtype=np.int64)
+    feats = rng.random((Tm, N, F))
+    direction = rng.choice([-1, 1], F)
+    cluster_of = np.arange(F) % N_CLUSTER
+    rng.shuffle(cluster_of)
+    ff12 = rng.integers(1, N_IND + 1, N)
+    size_grp = rng.choice(np.array(["mega", "large", "small"]), N)
+    K = N_IND + N_CLUSTER
+    A = rng.standard_normal((K, K))
+    C = A @ A.T / K
+    sig = rng.uniform(0.008, 0.03, N)
+    D = len(days)
+    f = (0.005 * np.linalg.cholesky(C) @ rng.standard_normal((K, D))).T      # [D, K]
+    e = sig[None, :] * rng.standard_normal((D, N))
+    return dict(days=days, month_ends=month_ends, ids=ids, feats=feats, direction=direction,
+                cluster_of=cluster_of, ff12=ff12, size_grp=size_grp, f_true=f, e=e, seed=seed)

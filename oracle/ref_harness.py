@@ -1,0 +1,129 @@
+"""Run the UNMODIFIED reference scripts from /root/reference on a synthetic panel (build container only).
+
+TEST INFRASTRUCTURE.  Used by oracle/make_golden.py to pin the numpy oracle against the reference
+itself; never imported by the product package, the GPU tests, smoke() or bench.py (the reference tree
+does not exist on the GPU box).
+
+Procedure: write the artefacts the scripts read under ``path + "Data/"``, stub
+the one off-path missing import (statsmodels ECDF, General_functions.py:14), wrap
+``General_functions.get_settings`` to set dates/grids, patch the pandas alias ``freq='M'`` ->
+``'ME'`` (PFML_Input_Data.py:231, rejected by pandas 3), then ``exec`` each script with the global
+``path`` exactly as Main.py:21-22 does.
+"""
+from __future__ import annotations
+
+import os
+import pickle
+import sqlite3
+import sys
+import types
+
+import numpy as np
+import pandas as pd
+
+REF = "/root/reference"
+
+
+def _import_general_functions():
+    if "statsmodels" not in sys.modules:
+        sm = types.ModuleType("statsmodels")
+        sd = types.ModuleType("statsmodels.distributions")
+        se = types.ModuleType("statsmodels.distributions.empirical_distribution")
+        se.ECDF = object
+        sys.modules.update({"statsmodels": sm, "statsmodels.distributions": sd,
+                            "statsmodels.distributions.empirical_distribution": se})
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+    import General_functions as GF
+    return GF
+
+
+def write_reference_inputs(panel, path):
+    """Write Factors_processed, FF_RF_monthly.csv, wealth_processed.csv, Barra_Cov.pkl, rff_w.csv."""
+    GF = _import_general_functions()
+    feats = GF.get_features(True)
+    data = os.path.join(path, "Data")
+    os.makedirs(data, exist_ok=True)
+    T, N, F = panel.feats.shape
+    assert F == len(feats)
+    me = pd.to_datetime(panel.month_ends)
+    rows = {
+        "id": np.tile(panel.ids, T),
+        "eom": np.repeat(me.strftime("%Y-%m-%d 00:00:00").values, N),
+        "sic": 0, "ff49": 0, "size_grp": "large", "me": 1.0, "crsp_exchcd": 1, "dolvol": 1.0,
+        "lambda": panel.lam.reshape(-1), "rvol_m": 0.0, "tr_ld0": panel.tr_ld0.reshape(-1),
+        "eom_ret": np.repeat((me + pd.offsets.MonthEnd(1)).strftime("%Y-%m-%d 00:00:00").values, N),
+        "ret_ld1": panel.ret_ld1.reshape(-1), "tr_ld1": 0.0, "mu_ld0": panel.mu_ld0.reshape(-1),
+        "ff12": "1", "valid": panel.valid.reshape(-1).astype(int),
+    }
+    df = pd.DataFrame(rows)
+    df = pd.concat([df, pd.DataFrame(panel.feats.reshape(T * N, F), columns=feats)], axis=1)
+    con = sqlite3.connect(os.path.join(data, "JKP_US_SP500.db"))
+    df.to_sql("Factors_processed", con, if_exists="replace", index=False)
+    con.close()
+    pd.DataFrame({"yyyymm": me.strftime("%Y%m").astype(int), "RF": panel.rf * 100.0}).to_csv(
+        os.path.join(data, "FF_RF_monthly.csv"), index=False)
+    pd.DataFrame({"eom": me, "wealth": panel.wealth, "mu_ld1": 0.0}).to_csv(
+        os.path.join(data, "wealth_processed.csv"), index=False)
+    names = [f"f{k}" for k in range(panel.fct_cov.shape[1])]
+    barra = {}
+    for t in range(T):
+        has = panel.barra_has[t]
+        ids = panel.ids[has].astype(int)
+        barra[me[t]] = {
+            "fct_load": pd.DataFrame(panel.fct_load[t][has], index=ids, columns=names),
+            "fct_cov": pd.DataFrame(panel.fct_cov[t], index=names, columns=names),
+            "ivol_vec": pd.Series(panel.ivol[t][has], index=ids),
+        }
+    with open(os.path.join(data, "Barra_Cov.pkl"), "wb") as f:
+        pickle.dump(barra, f)
+    pd.DataFrame(panel.W).to_csv(os.path.join(data, "rff_w.csv"))      # index column -> 'Unnamed: 0'
+
+
+def _settings_wrapper(GF, panel, p_vec, l_vec, start_year, end_yr, n_g=1):
+    orig = GF._orig_get_settings if hasattr(GF, "_orig_get_settings") else GF.get_settings
+    GF._orig_get_settings = orig
+
+    def get_settings():
+        settings, pf_set = orig()
+        settings["split"]["test_end"] = pd.Timestamp(panel.month_ends[-1])
+        settings["pf"]["dates"]["start_year"] = start_year
+        settings["pf"]["dates"]["end_yr"] = end_yr
+        settings["pf_ml"]["g_vec"] = [panel.meta.get("g", 0.05)] * n_g
+        settings["pf_ml"]["p_vec"] = list(p_vec)
+        settings["pf_ml"]["l_vec"] = list(l_vec)
+        pf_set["gamma_rel"] = panel.gamma_rel
+        pf_set["mu"] = panel.mu
+        pf_set["lb_hor"] = panel.lb
+        return settings, pf_set
+
+    GF.get_settings = get_settings
+
+
+def run_script(name, path, patches=()):
+    with open(os.path.join(REF, name)) as f:
+        src = f.read()
+    for a, b in patches:
+        assert a in src
+        src = src.replace(a, b)
+    glob = {"path": path if path.endswith("/") else path + "/", "__name__": "__main__"}
+    exec(compile(src, name, "exec"), glob)
+    return glob
+
+
+def run_pfml_input(panel, path, p_vec, l_vec=(0.0,), start_year=2013, end_yr=2013):
+    GF = _import_general_functions()
+    write_reference_inputs(panel, path)
+    _settings_wrapper(GF, panel, p_vec, l_vec, start_year, end_yr)
+    glob = run_script("PFML_Input_Data.py", path, patches=[("freq='M')", "freq='ME')")])
+    with open(os.path.join(path, "Data", "pfml_input_0.pkl"), "rb") as f:
+        out = pickle.load(f)[0]
+    return out, glob
+
+
+def run_search_coef(panel, path, p_vec, l_vec, start_year, end_yr):
+    GF = _import_general_functions()
+    _settings_wrapper(GF, panel, p_vec, l_vec, start_year, end_yr)
+    run_script("PFML_Search_Coef.py", path)
+    with open(os.path.join(path, "Data", "coef_dict_0.pkl"), "rb") as f:
+        return pickle.load(f)[0]

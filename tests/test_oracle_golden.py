@@ -1,0 +1,90 @@
+"""CPU: the numpy oracle (oracle/pfml_oracle.py) against vectors frozen from the reference itself.
+
+tests/golden/*.npz were produced by oracle/make_golden.py, which exec's the unmodified reference scripts
+from /root/reference on a synthetic panel.  Tolerances: 1e-10 relative (the oracle restates the same
+arithmetic in the same order; observed 1e-14)."""
+import os
+
+import numpy as np
+import pytest
+
+import pfml_oracle as O
+from conftest import GOLD, panel_from_golden, relerr
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(GOLD, "pfml_ref_small.npz"), allow_pickle=False)
+
+
+@pytest.fixture(scope="module")
+def funcs():
+    return np.load(os.path.join(GOLD, "funcs_ref.npz"))
+
+
+def test_date_step_matches_reference_script(gold, syn):
+    panel = panel_from_golden(gold, syn)
+    T, N, F = panel.feats.shape
+    rff_x = O.rff(panel.feats.reshape(T * N, F), panel.W).reshape(T, N, -1)
+    vs = O.vol_scale_panel(panel)
+    hot = gold["hot"]
+    assert (hot == panel.hot_months()).all()
+    for k in (0, len(hot) // 2, len(hot) - 1):
+        o = O.date_step(panel, int(hot[k]), rff_x, vs)
+        n = int(gold["n_d"][k])
+        assert o["signal_t"].shape[0] == n
+        for name in ("r_tilde", "denom", "risk", "tc"):
+            assert relerr(o[name], gold[name][k]) < 1e-10, name
+        assert relerr(o["signal_t"], gold["signal_t"][k, :n]) < 1e-10
+        # analytic properties the reference implies
+        assert relerr(o["risk"] + o["tc"], o["denom"]) < 1e-14
+        assert relerr(o["denom"], o["denom"].T) < 1e-9
+        assert np.linalg.eigvalsh(0.5 * (o["denom"] + o["denom"].T)).min() > -1e-10 * np.abs(o["denom"]).max()
+
+
+def test_search_coef_matches_reference_script(gold):
+    hot = gold["hot"]
+    month_ends = gold["panel_month_ends"][hot]
+    p_vec, l_vec, years = gold["p_vec"], gold["l_vec"], gold["years"]
+    coef = O.search_coef(gold["r_tilde"], gold["denom"], month_ends, years, p_vec, l_vec)
+    for y in years:
+        for p in p_vec:
+            ref = gold[f"coef_{y}_{p}"]
+            for j, l in enumerate(l_vec):
+                tol = 1e-9 if l > 0 else 1e-5        # lambda = 0 is condition-limited (quirk Q14)
+                assert relerr(coef[int(y)][int(p)][j], ref[j]) < tol
+
+
+def test_empty_window_raises(gold):
+    hot = gold["hot"]
+    month_ends = gold["panel_month_ends"][hot]
+    with pytest.raises(ValueError):
+        O.search_coef(gold["r_tilde"], gold["denom"], month_ends, [2030], gold["p_vec"], gold["l_vec"])
+
+
+def test_m_func_known_answer(funcs):
+    m = O.m_func(float(funcs["m_w"]), float(funcs["m_mu"]), float(funcs["m_rf"]), funcs["m_sigma"] * 10.0, 10.0,
+                 np.diag(funcs["m_lam"]), 10)
+    assert relerr(m, funcs["m_ref"]) < 1e-12
+    ev = np.linalg.eigvals(m).real
+    assert ev.min() > 0 and ev.max() < 1          # trading-speed matrix
+
+
+def test_weighted_cov_cor_known_answer(funcs):
+    assert relerr(O.weighted_cov_wt(funcs["wc_X"], funcs["wc_w"]), funcs["cov_ref"]) < 1e-13
+    cor = O.weighted_cor_wt(funcs["wc_X"], funcs["wc_w"])
+    assert relerr(cor, funcs["cor_ref"]) < 1e-13
+    assert (np.diag(cor) == 1.0).all()
+
+
+def test_ewma_vol_known_answer(funcs):
+    ev = O.ewma_vol(funcs["ev_x"], float(funcs["ev_lam"]), 63)
+    ref = funcs["ev_ref"]
+    assert (np.isnan(ev) == np.isnan(ref)).all()
+    assert np.nanmax(np.abs(ev - ref)) < 1e-15
+    assert np.isnan(O.ewma_vol(funcs["ev_x"][:60], 0.99, 63)).all()      # n <= start
+
+
+def test_feature_index_map_bit_exact(funcs):
+    for p in (4, 8, 16):
+        assert (O.pfml_feat_idx(p, 16) == funcs[f"feat_idx_{p}"]).all()
