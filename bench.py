@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""bench.py -- PFML date-steps/sec (r_tilde + denom, N=500, p=1024) on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--dates B]
+
+A "step" is one batch of B date-steps (one iteration each of the loop PFML_Input_Data.py:318-491: Sigma,
+Lambda, m_func, standardise, chains, solves, r_tilde / risk / tc / denom) on one GPU.  Dates are independent,
+so ranks shard them with no data-path collective (weak scaling: every rank runs its own B dates per step).
+
+Printed JSON line (rank 0): value = whole-job date-steps/s with inputs resident in HBM; e2e = the same through
+pfml_date_steps_host (pinned HOST buffers in, HOST buffers out, H2D/D2H inside the timed region); roofline = the
+dominant kernel (the batched FP64 DMMA GEMM) against the FP64 GEMM peak measured in this run; cpu_baseline = the
+numpy oracle (a port of the reference's algorithm) on the host cores.  --impl reference times only that CPU arm.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+PKG = "jkmp22-machine-learning-and-the-implementable-efficient-frontier-replication_b200"
+
+N_STOCKS, P_FEAT = 500, 1024
+METRIC = "PFML date-steps/sec (r_tilde+denom, N=500, p=1024)"
+UNIT = "date-steps/s"
+
+
+def official_flops_per_date(n=N_STOCKS, P=P_FEAT + 1):
+    """SURVEY.md section 8(d), 'Date-step total (reduced, official)'."""
+    a9 = 2 * n * n * P + 2 * n * P * P + 2 * n * P
+    chain = 22 * n ** 3 + 24 * n * n * P
+    lu = 2 * (2 / 3 * n ** 3 + 2 * n * n * P)
+    mf = 23 * n ** 3
+    return dict(total=a9 + chain + lu + mf, denom=a9, chain=chain, solve=lu, m_func=mf)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for k, nm in enumerate(names):
+                if len(r) > 4 + k and r[4 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max((float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()), default=None),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_bench_panel(syn, B, seed):
+    return syn.make_panel(N=N_STOCKS, T=syn.LB + 2 + B, p=P_FEAT, seed=seed, g=float(np.exp(-3.0)))
+
+
+def cpu_dates_per_sec(syn, budget_s=20.0, max_dates=8, seed=101):
+    """Oracle (numpy port of the reference algorithm, all host BLAS threads) on a bounded sample of the workload."""
+    import pfml_oracle as O
+    panel = make_bench_panel(syn, max_dates, seed)
+    T, N, F = panel.feats.shape
+    rff_x = O.rff(panel.feats.reshape(T * N, F), panel.W).reshape(T, N, -1)      # a1, excluded like on the GPU side
+    vs = O.vol_scale_panel(panel)                                               # a2
+    hot = list(panel.hot_months())
+    t0 = time.perf_counter()
+    done = 0
+    for t in hot:
+        O.date_step(panel, int(t), rff_x, vs)
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return done / dt, done, dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    syn = importlib.import_module(PKG + ".synthetic")
+    cores = os.cpu_count()
+    per_step = 2
+    import pfml_oracle as O
+    panel = make_bench_panel(syn, per_step, 101)
+    T, N, F = panel.feats.shape
+    rff_x = O.rff(panel.feats.reshape(T * N, F), panel.W).reshape(T, N, -1)
+    vs = O.vol_scale_panel(panel)
+    hot = [int(t) for t in panel.hot_months()]
+
+    def step():
+        for t in hot:
+            O.date_step(panel, t, rff_x, vs)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    val = per_step * args.steps / dt
+    sample = f"{per_step} date-steps per step of the N=500, p=1024 workload (panel-level RFF / vol_scale excluded, as on the GPU arm)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "PFML date-step N=500 p=1024 (P=1025), lb=11, 10 m_func iterations", "dates_per_step": per_step},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference algorithm restated in numpy/scipy (oracle/pfml_oracle.py), OpenBLAS threads = all host cores; "
+                "the reference's pandas per-column standardisation is replaced by vectorised numpy, so this CPU arm is "
+                "faster than the reference script itself"}))
+
+
+def measure_fp64_peak(torch, dev):
+    n = 8192
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    b = torch.randn(n, n, dtype=torch.float64, device=dev)
+    for _ in range(2):
+        a @ b
+    torch.cuda.synchronize(dev)
+    best = 1e30
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); a @ b; e1.record()
+        torch.cuda.synchronize(dev)
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    return 2 * n ** 3 / best * 1e-9        # TFLOP/s
+
+
+def run_ours(args, rank, world, local_rank):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    syn = importlib.import_module(PKG + ".synthetic")
+    device_mod = importlib.import_module(PKG + ".device")
+    host_mod = importlib.import_module(PKG + ".host")
+    lib = importlib.import_module(PKG + "._lib").load()
+    dev = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(dev)
+    B = args.dates
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    panel = make_bench_panel(syn, B, seed=7 + rank)
+    months = [int(t) for t in panel.hot_months()]
+    assert len(months) == B
+    dpanel = device_mod.DevicePanel(panel, dev)
+    sel, n_sel, n_max, NP = device_mod.universe(panel, months)
+    runner = device_mod.DateStepRunner(dpanel, B, n_max)
+    runner.set_batch(months, sel, n_sel)
+
+    if args.gemm_only:
+        # the dominant launch shape in isolation (Horner step: m~ [n x n] @ Z [n x P], batch = dates), for ncu --set full
+        A = torch.randn(B, NP, NP, dtype=torch.float64, device=dev)
+        Z = torch.randn(B, NP, 1032, dtype=torch.float64, device=dev)
+        D = torch.empty(B, NP, 1032, dtype=torch.float64, device=dev)
+        P = P_FEAT + 1
+        evs = []
+        for i in range(args.warmup + args.steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = lib.pfml_dgemm_batched(0, 0, NP, P, NP, 1.0, C.c_void_p(A.data_ptr()), NP, NP * NP, C.c_void_p(Z.data_ptr()), 1032,
+                                        NP * 1032, 0.0, C.c_void_p(D.data_ptr()), 1032, NP * 1032, B,
+                                        C.c_void_p(torch.cuda.current_stream().cuda_stream))
+            e1.record()
+            assert rc == 0
+            evs.append((e0, e1))
+        torch.cuda.synchronize(dev)
+        ms = min(a.elapsed_time(b) for a, b in evs[args.warmup:])
+        ref = torch.matmul(A[0], Z[0, :, :P])
+        err = float((D[0, :, :P] - ref).abs().max() / ref.abs().max())
+        print(json.dumps({"gemm_only": True, "shape": [B, NP, P, NP], "ms": ms,
+                          "executed_tflops": 2.0 * B * NP * P * NP / ms * 1e-9, "rel_err_vs_cublas": err}))
+        return
+
+    # ---- value: inputs resident in HBM -------------------------------------------------------------
+    for _ in range(args.warmup):
+        runner.run()
+    if args.profile_only:
+        for _ in range(args.steps):
+            runner.run()
+        torch.cuda.synchronize(dev)
+        print(json.dumps({"profile_only": True, "dates": B, "steps": args.steps, "launches_per_step":
+                          lib.pfml_launch_count() // (args.warmup + args.steps)}))
+        return
+    barrier()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    l0 = lib.pfml_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        runner.run()
+    e1.record()
+    barrier()
+    launches = lib.pfml_launch_count() - l0
+    clocks = sampler.stop() if sampler else None
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    value = world * B * args.steps / (ms_total * 1e-3)
+    assert int(runner.status.abs().sum().item()) == 0, "numerical failure flag set"
+
+    # ---- live per-kernel accounting (CUDA events around every launch group, same steps) ------------
+    nt = lib.pfml_prof_ntags()
+    pms, pfl, pln = (np.zeros(nt) for _ in range(3))
+    lib.pfml_prof_enable(1)
+    for _ in range(args.steps):
+        runner.run()
+    lib.pfml_prof_collect(C.c_void_p(pms.ctypes.data), C.c_void_p(pfl.ctypes.data), C.c_void_p(pln.ctypes.data))
+    lib.pfml_prof_enable(0)
+    names = [lib.pfml_prof_tag_name(i).decode() for i in range(nt)]
+
+    # ---- e2e: host buffers in / out through pfml_date_steps_host ------------------------------------
+    blk = host_mod.HostBlock(panel, months, pin=True)
+    for _ in range(max(1, min(args.warmup, 2))):
+        blk.run(chunk=args.chunk, device=local_rank)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        blk.run(chunk=args.chunk, device=local_rank)
+    torch.cuda.synchronize(dev)
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_val = world * B * args.steps / float(dt.item())
+    assert int(blk.status.abs().sum()) == 0
+    chk = float(np.max(np.abs(blk.out["denom"][0].numpy() - runner.denom[0].cpu().numpy())))
+
+    if rank != 0:
+        return
+    # ---- roofline of the dominant kernel -------------------------------------------------------------
+    peak = measure_fp64_peak(torch, dev)
+    off = official_flops_per_date()
+    gemm_ms = pms[0] / args.steps                      # all DMMA GEMM launches of one step
+    total_stage_ms = sum(pms[1:7]) / args.steps
+    achieved = off["total"] * B / (gemm_ms * 1e-3) * 1e-12
+    executed = pfl[0] / args.steps / (gemm_ms * 1e-3) * 1e-12
+    traffic = None
+    ncu_json = os.path.join(ROOT, "profiles", "ncu_summary.json")
+    if os.path.exists(ncu_json):
+        try:
+            traffic = json.load(open(ncu_json)).get("dmma_gemm_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    stage_map = {"m_func": off["m_func"], "chain_nxn": 22 * N_STOCKS ** 3, "horner_nxP": 24 * N_STOCKS ** 2 * (P_FEAT + 1),
+                 "solve": off["solve"], "denom": off["denom"]}
+    stages = {}
+    for i in range(1, 7):
+        st_ms = pms[i] / args.steps
+        stages[names[i]] = {"ms_per_step": round(st_ms, 3), "share": round(st_ms / total_stage_ms, 4)}
+        if names[i] in stage_map:
+            stages[names[i]]["algorithmic_tflops"] = round(stage_map[names[i]] * B / (st_ms * 1e-3) * 1e-12, 2)
+    cpu_v, cpu_n, cpu_dt = cpu_dates_per_sec(syn)
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "PFML date-step N=500 p=1024 (P=1025), lb=11, 10 m_func iterations (BASELINE configs[2] at the metric's p)",
+                   "dates_per_step_per_gpu": B, "parallelism": f"dates sharded over {world} GPU(s), no data-path collective",
+                   "l2": "per-step working set ~%.1f GB >> 126 MB L2 (inputs larger than L2)" % (runner.ws_bytes / 1e9)},
+        "clocks": clocks,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(blk.h2d_bytes), "d2h_bytes_per_step": int(blk.d2h_bytes),
+                "outputs": "r_tilde, denom, risk, tc, signal_t (everything PFML_Input_Data.py stores per date)",
+                "chunk": args.chunk, "max_abs_diff_vs_resident_path": chk},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "tensor", "kernel": "pfml::gemm_kernel (batched FP64 DMMA GEMM, all launches of a step)",
+                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                     "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, best of 5, measured in this run "
+                                    "(MEASURED_PEAKS.json has no FP64 figure; DMMA issue peak 37.05 TFLOP/s, profiles/r01_fp64_peak_microbench.log)",
+                     "algorithmic_flops_per_date": off["total"], "executed_tflops": executed,
+                     "gemm_ms_per_step": gemm_ms, "gemm_launches_per_step": pln[0] / args.steps,
+                     "gemm_share_of_step": gemm_ms / (ms_total / args.steps)},
+        "stages": stages,
+        "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                         "sample": f"{cpu_n} date-steps of the same N=500, p=1024 workload in {cpu_dt:.1f} s (numpy oracle, all host BLAS threads)"},
+    }
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dates", type=int, default=148, help="date-steps per step per GPU")
+    ap.add_argument("--chunk", type=int, default=37, help="dates per device chunk in the host entry point")
+    ap.add_argument("--profile-only", action="store_true", help="resident-path steps only (for ncu launch lists)")
+    ap.add_argument("--gemm-only", action="store_true", help="the dominant GEMM shape alone (for ncu --set full)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
