@@ -91,6 +91,21 @@ size_t pfml_inverse_workspace_bytes(int B, int n);
 int pfml_inverse_batched(int B, int n, const double* A, double* Ainv, int* status, void* workspace,
                          size_t workspace_bytes, void* stream);
 
+/* The same inverse for callers that may not allocate device memory (no counterpart in the reference: this
+ * entry point exists only for embedding the library).  Some hosts cannot call cudaMalloc where they need the
+ * inverse -- inside a latency-critical section, inside a plugin whose process-wide memory pool is owned by
+ * someone else, or simply without a spare 3*B*NP*NP-double buffer for the workspace above.  Here the work
+ * matrices are a fixed 12 MiB array inside the library image (resident on every GPU that loads the library,
+ * until the process exits), so only inputs and outputs are passed.
+ *   limit   B * NP * NP <= PFML_INVERSE_STATIC_MAX_ELEMS with NP = pfml_padded_n(n); beyond it the call returns
+ *           -3 with a message and launches nothing;
+ *   sharing one array per GPU, reused by every call and never cleared (no step depends on old contents); calls
+ *           that can overlap on one GPU race -- keep them on one stream or serialise them;
+ *   set-up  the first call on each GPU resolves the array's device address; make it before any stream capture.
+ * Allocates nothing: no cudaMalloc, cudaFree or allocating library routine on this path. */
+#define PFML_INVERSE_STATIC_MAX_ELEMS (1 << 19)
+int pfml_inverse_batched_static(int B, int n, const double* A, double* Ainv, int* status, void* stream);
+
 /* Whole block through HOST buffers (the end-to-end call a drop-in user makes): uploads the block's inputs,
  * runs a1 + a2 + B date-steps on the device, downloads the outputs.  feats [T*N][F], W [F][p/2], tr_ld0/
  * mu_ld0/lam/ret_ld1/ivol [T*N], fct_load [T*N][K], fct_cov [T][K][K], barra_has [T*N] (uint8, may be NULL),

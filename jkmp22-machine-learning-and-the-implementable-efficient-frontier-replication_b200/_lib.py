@@ -65,6 +65,7 @@ SIGNATURES = {
     "pfml_inverse_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "pfml_inverse_batched": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                        C.c_void_p]),
+    "pfml_inverse_batched_static": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "pfml_date_steps_host": (C.c_int, [C.POINTER(HostBlockStruct), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_int, C.c_int]),
