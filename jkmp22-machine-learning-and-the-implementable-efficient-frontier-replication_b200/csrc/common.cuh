@@ -49,6 +49,7 @@ struct GemmP {
   double* D = nullptr;       long ldd = 0; long sD = 0;
   const double* E = nullptr; long lde = 0; long sE = 0;
   double* D2 = nullptr; const double* E2 = nullptr;
+  double* DT = nullptr; long ldt = 0;   // optional transposed copy DT[c][r] = D[r][c] (batch stride sD)
   int M = 0, N = 0, K = 0;
   bool a_kinner = true, b_kinner = false;
   double alpha = 1.0, beta = 0.0, diag = 0.0;

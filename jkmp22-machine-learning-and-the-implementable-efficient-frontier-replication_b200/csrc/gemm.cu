@@ -173,6 +173,7 @@ gemm_kernel(const GemmP p) {
   double* D = p.D + (long)z * p.sD;   // may alias E / E2 (element-wise in-place updates)
   const double* E = p.E ? p.E + (long)z * p.sE : nullptr;
   double* D2 = p.D2 ? p.D2 + (long)z * p.sD : nullptr;
+  double* DT = p.DT ? p.DT + (long)z * p.sD : nullptr;
   const double* E2 = p.E2 ? p.E2 + (long)z * p.sD : nullptr;
   const double* rs = p.rs ? p.rs + (long)z * p.s_rs : nullptr;
   const double* cs = p.cs ? p.cs + (long)z * p.s_cs : nullptr;
@@ -202,6 +203,7 @@ gemm_kernel(const GemmP p) {
         }
         D[(long)r * p.ldd + cc] = v;
         if (p.sym && cc != r) D[(long)cc * p.ldd + r] = v;
+        if (DT) DT[(long)cc * p.ldt + r] = v;
         if (D2) {
           double v2 = v + E2[(long)r * p.ldd + cc];
           D2[(long)r * p.ldd + cc] = v2;

@@ -333,78 +333,122 @@ __global__ void m_from_mtilde_kernel(int n, int NP, const double* __restrict__ m
 }
 
 // ------------------------------------------------------------------------------------------------
-// In-place Gauss-Jordan inverse with partial (row) pivoting of one 64x64 diagonal block per CTA.
+// Gauss-Jordan inverse of one NB x NB diagonal block per CTA (NB = 64 or 128), matrix held in REGISTERS:
+// thread (ti, tj) owns the 4x4 tile rows 4ti.., cols 4tj..; per pivot step the owners of the pivot row and of
+// column k publish them through double-buffered shared memory, everybody updates its 16 elements.
+// PIVOT = false (SPD blocks of m_tilde's fixed point): pivot k is row k, one barrier per step.
+// PIVOT = true  (general blocks): implicit partial pivoting -- the pivot row is the unused row with the largest
+// |a[r][k]|, rows are never moved, the permutation is undone when the result is written
+// (Ainv[k][p_c] = stored[p_k][c]).  Threads are numbered tid = tj * (NB/4) + ti so that the owners of a column
+// sit in one warp (NB = 128) / half-warp (NB = 64) and the pivot search is a shuffle reduction.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-base_inverse_kernel(int NP, const double* __restrict__ src, double* __restrict__ dst, int off, int* __restrict__ status) {
-  __shared__ double a[BASE][BASE + 1];
-  __shared__ double prow[BASE], pcol[BASE];
-  __shared__ int piv[BASE];
+template <int NB, bool PIVOT>
+__global__ void __launch_bounds__((NB / 4) * (NB / 4))
+gj_inverse_kernel(int NP, const double* __restrict__ src, double* __restrict__ dst, int off, int* __restrict__ status) {
+  constexpr int TD = NB / 4;               // threads per tile dimension
+  __shared__ double prow[2][NB], pcol[2][NB];
+  __shared__ int s_piv[NB];                // pivot row of step k
+  __shared__ int s_pinv[NB];               // step at which row r was the pivot
   __shared__ int bad;
   const int b = blockIdx.x, tid = threadIdx.x;
+  const int ti = tid % TD, tj = tid / TD;
   const double* S = src + (long)b * NP * NP + (long)off * NP + off;
   double* Dp = dst + (long)b * NP * NP + (long)off * NP + off;
   if (tid == 0) bad = 0;
-  for (int e = tid; e < BASE * BASE; e += 256) a[e / BASE][e % BASE] = S[(long)(e / BASE) * NP + (e % BASE)];
+  double a[4][4];
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+    const double2* s2 = reinterpret_cast<const double2*>(S + (long)(4 * ti + r) * NP + 4 * tj);
+    double2 v0 = s2[0], v1 = s2[1];
+    a[r][0] = v0.x; a[r][1] = v0.y; a[r][2] = v1.x; a[r][3] = v1.y;
+  }
+  unsigned used = 0;                       // bit r: my row 4ti+r has been a pivot row
+  for (int k = 0; k < NB; k++) {
+    const int buf = k & 1;
+    const int kj = k >> 2, kc = k & 3;
+    int p = k;
+    if (PIVOT) {
+      if (tj == kj) {                      // owners of column k: one (half-)warp
+        double best = -1.0;
+        int bi = -1;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+          double akc = a[r][0];                      // static register indexing only (no local-memory array)
+#pragma unroll
+          for (int c = 1; c < 4; c++) akc = (c == kc) ? a[r][c] : akc;
+          const double v = fabs(akc);                // NaN never wins a comparison: an all-NaN column is flagged
+          if (!((used >> r) & 1u) && v > best) { best = v; bi = 4 * ti + r; }
+        }
+        const unsigned mask = (TD == 32) ? 0xffffffffu : (0xffffu << (tid & 16));
+#pragma unroll
+        for (int o = TD / 2; o > 0; o >>= 1) {
+          const double ob = __shfl_xor_sync(mask, best, o, TD);
+          const int oi = __shfl_xor_sync(mask, bi, o, TD);
+          if (ob > best || (ob == best && oi >= 0 && (bi < 0 || oi < bi))) { best = ob; bi = oi; }
+        }
+        if (ti == 0) {
+          s_piv[k] = bi < 0 ? k : bi;
+          if (!(best > 0.0) || !isfinite(best)) bad = 1;
+        }
+      }
+      __syncthreads();
+      p = s_piv[k];
+    } else if (tid == 0) {
+      s_piv[k] = k;
+    }
+    const int pi = p >> 2, pr = p & 3;
+    if (ti == pi) {                        // owners of the pivot row publish it
+#pragma unroll
+      for (int r = 0; r < 4; r++)
+        if (r == pr) {
+#pragma unroll
+          for (int c = 0; c < 4; c++) prow[buf][4 * tj + c] = a[r][c];
+        }
+      used |= 1u << pr;
+      if (tj == 0) s_pinv[p] = k;
+    }
+    if (tj == kj) {                        // owners of column k publish it
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        double akc = a[r][0];
+#pragma unroll
+        for (int c = 1; c < 4; c++) akc = (c == kc) ? a[r][c] : akc;
+        pcol[buf][4 * ti + r] = akc;
+      }
+    }
+    __syncthreads();
+    const double pv = prow[buf][k];
+    if (!PIVOT && tid == 0 && (!(fabs(pv) > 0.0) || !isfinite(pv))) bad = 1;
+    const double ipv = 1.0 / pv;
+    double q[4], f[4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) q[c] = (4 * tj + c == k) ? ipv : prow[buf][4 * tj + c] * ipv;
+#pragma unroll
+    for (int r = 0; r < 4; r++) f[r] = pcol[buf][4 * ti + r];
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      const bool is_p = (4 * ti + r == p);
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        const double old = (4 * tj + c == k) ? 0.0 : a[r][c];
+        a[r][c] = is_p ? q[c] : old - f[r] * q[c];
+      }
+    }
+    // double-buffered prow/pcol: the next step writes the other buffer, and its barrier orders this step's reads
+  }
   __syncthreads();
-  const int ri = tid >> 2, c0 = (tid & 3) * 16;
-  for (int k = 0; k < BASE; k++) {
-    if (tid < 32) {
-      double best = -1.0;
-      int bi = k;
-      for (int r = k + tid; r < BASE; r += 32) {
-        double v = fabs(a[r][k]);
-        if (v > best) { best = v; bi = r; }
-      }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        double ob = __shfl_xor_sync(0xffffffffu, best, o);
-        int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
-      }
-      if (tid == 0) {
-        piv[k] = bi;
-        if (!(best > 0.0) || !isfinite(best)) bad = 1;
-      }
-    }
-    __syncthreads();
-    const int p = piv[k];
-    if (p != k && tid < BASE) {
-      double tmp = a[k][tid];
-      a[k][tid] = a[p][tid];
-      a[p][tid] = tmp;
-    }
-    __syncthreads();
-    if (tid < BASE) {
-      const double ip = 1.0 / a[k][k];
-      prow[tid] = (tid == k) ? ip : a[k][tid] * ip;
-      pcol[tid] = a[tid][k];
-    }
-    __syncthreads();
-    if (ri == k) {
+  for (int r = 0; r < 4; r++) {
+    const int orow = PIVOT ? s_pinv[4 * ti + r] : 4 * ti + r;
+    if (PIVOT) {
 #pragma unroll
-      for (int c = 0; c < 16; c++) a[k][c0 + c] = prow[c0 + c];
+      for (int c = 0; c < 4; c++) Dp[(long)orow * NP + s_piv[4 * tj + c]] = a[r][c];
     } else {
-      const double f = pcol[ri];
-#pragma unroll
-      for (int c = 0; c < 16; c++) {
-        const int cc = c0 + c;
-        const double old = (cc == k) ? 0.0 : a[ri][cc];
-        a[ri][cc] = old - f * prow[cc];
-      }
+      double2* d2 = reinterpret_cast<double2*>(Dp + (long)orow * NP + 4 * tj);
+      d2[0] = make_double2(a[r][0], a[r][1]);
+      d2[1] = make_double2(a[r][2], a[r][3]);
     }
-    __syncthreads();
   }
-  for (int k = BASE - 1; k >= 0; k--) {
-    const int p = piv[k];
-    if (p != k && tid < BASE) {
-      double tmp = a[tid][k];
-      a[tid][k] = a[tid][p];
-      a[tid][p] = tmp;
-    }
-    __syncthreads();
-  }
-  for (int e = tid; e < BASE * BASE; e += 256) Dp[(long)(e / BASE) * NP + (e % BASE)] = a[e / BASE][e % BASE];
   if (tid == 0 && bad && status) atomicOr(status + b, 1);
 }
 
@@ -591,8 +635,17 @@ int m_from_mtilde(int B, int n, int NP, const double* mt, const double* isl, con
   return 0;
 }
 
-int base_inverse(int B, int NP, const double* src, double* dst, int off, int* status, cudaStream_t s) {
-  base_inverse_kernel<<<B, 256, 0, s>>>(NP, src, dst, off, status);
+int base_inverse(int B, int NP, const double* src, double* dst, int off, int size, bool spd, int* status, cudaStream_t s) {
+  if (size == 64) {
+    if (spd) gj_inverse_kernel<64, false><<<B, 256, 0, s>>>(NP, src, dst, off, status);
+    else gj_inverse_kernel<64, true><<<B, 256, 0, s>>>(NP, src, dst, off, status);
+  } else if (size == 128) {
+    if (spd) gj_inverse_kernel<128, false><<<B, 1024, 0, s>>>(NP, src, dst, off, status);
+    else gj_inverse_kernel<128, true><<<B, 1024, 0, s>>>(NP, src, dst, off, status);
+  } else {
+    set_error("base_inverse: unsupported block size %d", size);
+    return -2;
+  }
   PFML_CHECK_LAUNCH();
   return 0;
 }

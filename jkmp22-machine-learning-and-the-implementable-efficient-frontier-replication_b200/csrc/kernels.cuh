@@ -22,7 +22,8 @@ struct PanelView {
 };
 
 constexpr int KP = 32;         // factor count padded (K <= 32)
-constexpr int BASE = 64;       // base block of the recursive inversion
+constexpr int BASE = 64;       // padding granularity of n (blocks of the recursive inversion are multiples of it)
+constexpr int BASE_MAX = 128;  // largest block inverted by one CTA (register-resident Gauss-Jordan)
 constexpr int NSCAL = 8;       // per-date scalars: 0 gamma/w... see prep_vectors
 constexpr int NORM_CHUNKS = 16;
 
@@ -62,7 +63,7 @@ int row_scale(int B, int rows, int cols, long ld, long stride, const double* in,
               long ldo, long stride_o, cudaStream_t s);
 int m_from_mtilde(int B, int n, int NP, const double* mt, const double* isl, const double* sl, double* m_out, cudaStream_t s);
 
-int base_inverse(int B, int NP, const double* src, double* dst, int off, int* status, cudaStream_t s);
+int base_inverse(int B, int NP, const double* src, double* dst, int off, int size, bool spd, int* status, cudaStream_t s);
 int gemv_t(int B, int rows, int cols, const double* A, long ld, long sA, const double* v, long sv, double* out, long so,
            cudaStream_t s);
 int check_finite_status(int B, const double* sc, int* status, cudaStream_t s);

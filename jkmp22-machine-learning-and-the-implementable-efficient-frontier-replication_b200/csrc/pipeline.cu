@@ -102,10 +102,10 @@ struct Carver {
 //   M^-1 = [A^-1 + W S^-1 V, -W S^-1; -S^-1 V, S^-1],  W = A^-1 B, V = C A^-1.
 // Wk (destroyed) holds M, X receives M^-1, T1 holds W and V.  All [B][NP][NP].
 // ------------------------------------------------------------------------------------------------
-struct InvCtx { int B, NP; double *Wk, *X, *T1; int* status; cudaStream_t s; };
+struct InvCtx { int B, NP; double *Wk, *X, *T1; int* status; cudaStream_t s; bool spd = false; };
 
 static int inv_rec(const InvCtx& c, int off, int size) {
-  if (size <= BASE) return base_inverse(c.B, c.NP, c.Wk, c.X, off, c.status, c.s);
+  if (size <= BASE_MAX) return base_inverse(c.B, c.NP, c.Wk, c.X, off, size, c.spd, c.status, c.s);
   const int nb = size / BASE, h = ((nb + 1) / 2) * BASE, r = size - h;
   const long NP = c.NP, NN = NP * NP;
   auto at = [&](double* base, int r0, int c0) { return base + (long)r0 * NP + c0; };
@@ -117,6 +117,28 @@ static int inv_rec(const InvCtx& c, int off, int size) {
   g.A = at(c.X, off, off); g.B = at(c.Wk, off, off + h); g.D = at(c.T1, off, off + h);
   g.M = h; g.N = r; g.K = h;
   PFML_TRY(gemm(g, c.B, c.s));
+  if (c.spd) {
+    // symmetric positive definite: C = B', V = W', X21 = X12'; S and X11 are symmetric (lower tiles + mirror)
+    // S = D - B' * W   (in place over D)
+    g.A = at(c.Wk, off, off + h); g.a_kinner = false; g.B = at(c.T1, off, off + h); g.D = at(c.Wk, off + h, off + h);
+    g.E = g.D; g.alpha = -1.0; g.beta = 1.0; g.sym = 1;
+    g.M = r; g.N = r; g.K = h;
+    PFML_TRY(gemm(g, c.B, c.s));
+    PFML_TRY(inv_rec(c, off + h, r));
+    // X12 = -W * X22, mirrored into X21
+    g.a_kinner = true; g.sym = 0; g.E = nullptr; g.beta = 0.0;
+    g.A = at(c.T1, off, off + h); g.B = at(c.X, off + h, off + h); g.D = at(c.X, off, off + h);
+    g.DT = at(c.X, off + h, off); g.ldt = NP;
+    g.M = h; g.N = r; g.K = r;
+    PFML_TRY(gemm(g, c.B, c.s));
+    // X11 = X11 - X12 * W'
+    g.DT = nullptr;
+    g.A = at(c.X, off, off + h); g.B = at(c.T1, off, off + h); g.b_kinner = true; g.D = at(c.X, off, off);
+    g.E = g.D; g.beta = 1.0; g.sym = 1;
+    g.M = h; g.N = h; g.K = r;
+    PFML_TRY(gemm(g, c.B, c.s));
+    return 0;
+  }
   // V = C * X11
   g.A = at(c.Wk, off + h, off); g.B = at(c.X, off, off); g.D = at(c.T1, off + h, off);
   g.M = r; g.N = h; g.K = h;
@@ -167,7 +189,7 @@ static int mtilde(int B, int NP, int iterations, const MtBufs& m, int* status, c
   PFML_TRY(gemm(g, B, s));
   PFML_TRY(copy2(B, NN, m.Mdb, m.Ya, m.Wk, s));
   double *Ya = m.Ya, *Yb = m.Yb;
-  InvCtx ic{B, NP, m.Wk, m.Xinv, m.T1, status, s};
+  InvCtx ic{B, NP, m.Wk, m.Xinv, m.T1, status, s, true};
   for (int k = 0; k < DB_ITERS; k++) {
     PFML_TRY(inverse(ic));
     PFML_TRY(db_norms(B, NP, m.Mdb, m.Xinv, m.part, m.sc, s));
@@ -188,7 +210,7 @@ static int mtilde(int B, int NP, int iterations, const MtBufs& m, int* status, c
   PFML_TRY(mt0_from_sqrt(B, NP, m.x, Ya, mt, s));
   for (int it = 0; it < iterations; it++) {
     PFML_TRY(fp_build(B, NP, m.x, m.yv, mt, m.sgr, m.Wk, s));
-    InvCtx fc{B, NP, m.Wk, other, m.T1, status, s};
+    InvCtx fc{B, NP, m.Wk, other, m.T1, status, s, true};
     PFML_TRY(inverse(fc));
     double* t = mt; mt = other; other = t;
   }
