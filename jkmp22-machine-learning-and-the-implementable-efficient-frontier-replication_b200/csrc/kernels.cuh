@@ -26,6 +26,9 @@ constexpr int BASE = 64;       // padding granularity of n (blocks of the recurs
 constexpr int BASE_MAX = 128;  // largest block inverted by one CTA (register-resident Gauss-Jordan)
 constexpr int NSCAL = 8;       // per-date scalars: 0 gamma/w... see prep_vectors
 constexpr int NORM_CHUNKS = 16;
+// trapezoid quadrature of the semicircle Stieltjes integral (stieltjes.cu): s_j = SQ_SMIN + j * SQ_H
+constexpr int SQ_NODES = 121;
+constexpr double SQ_H = 0.5, SQ_SMIN = -36.0;
 
 struct BatchVecs {             // per-date vectors, all [B][NP] unless noted
   double* sl;      // sqrt(lambda)            (pad 1)
@@ -67,6 +70,11 @@ int base_inverse(int B, int NP, const double* src, double* dst, int off, int siz
 int gemv_t(int B, int rows, int cols, const double* A, long ld, long sA, const double* v, long sv, double* out, long so,
            cudaStream_t s);
 int check_finite_status(int B, const double* sc, int* status, cudaStream_t s);
+
+// m_tilde_0 by quadrature + Woodbury in the factor form (stieltjes.cu)
+long stj_ldg(int K);
+int mt0_stieltjes(int B, int NP, int K, const int* nsel, const BatchVecs& v, double* Ut, double* Ev, double* G, double* mt,
+                  int* status, cudaStream_t s);
 
 // panel-level helpers
 int gt_panel(long n, const double* tr_ld0, const double* mu_ld0, double* gt, cudaStream_t s);

@@ -178,6 +178,8 @@ struct MtBufs {
   double *x, *sgr, *yv, *Mdb, *Wk, *Xinv, *T1, *Ya, *Yb, *mt, *part, *sc;
 };
 
+static int fixed_point(int B, int NP, int iterations, const MtBufs& m, int* status, cudaStream_t s, double** mt_out);
+
 static int mtilde(int B, int NP, int iterations, const MtBufs& m, int* status, cudaStream_t s, double** mt_out) {
   const long NN = (long)NP * NP;
   GemmP g;
@@ -206,8 +208,13 @@ static int mtilde(int B, int NP, int iterations, const MtBufs& m, int* status, c
     double* t = Ya; Ya = Yb; Yb = t;
   }
   if (status) PFML_TRY(check_finite_status(B, m.sc, status, s));
+  PFML_TRY(mt0_from_sqrt(B, NP, m.x, Ya, m.mt, s));
+  return fixed_point(B, NP, iterations, m, status, s, mt_out);
+}
+
+// the `iterations` steps m~ <- inv(x + y - m~ o sigma_gr) of General_functions.py:959-960, starting from m.mt
+static int fixed_point(int B, int NP, int iterations, const MtBufs& m, int* status, cudaStream_t s, double** mt_out) {
   double *mt = m.mt, *other = m.Xinv;
-  PFML_TRY(mt0_from_sqrt(B, NP, m.x, Ya, mt, s));
   for (int it = 0; it < iterations; it++) {
     PFML_TRY(fp_build(B, NP, m.x, m.yv, mt, m.sgr, m.Wk, s));
     InvCtx fc{B, NP, m.Wk, other, m.T1, status, s, true};
@@ -225,13 +232,13 @@ struct StepWs {
   int B, NP, P, nt; long ldP;
   BatchVecs v;
   MtBufs m;
-  double *XC, *XCl1;
+  double *XC, *XCl1, *Ut, *Ev, *G;
   double *St, *Za, *Zb, *Nn, *Nl1, *OM, *BS, *OMC;
   double *risk_tmp, *tc_tmp;
   size_t bytes;
 };
 
-static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, bool need_risk, bool need_tc) {
+static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int K, bool need_risk, bool need_tc) {
   StepWs w{};
   w.B = B; w.NP = NP; w.P = P; w.nt = nt;
   w.ldP = round_up(P, 8);
@@ -255,7 +262,12 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, boo
   w.m.part = c.take<double>((size_t)B * NORM_CHUNKS * 3);
   w.m.sc = c.take<double>((size_t)B * 8);
   w.XC = c.take<double>(BNN); w.XCl1 = c.take<double>(BNN);
+  w.Ut = c.take<double>((size_t)B * NP * KP);
+  w.Ev = c.take<double>((size_t)B * NP);
   w.St = c.take<double>((size_t)nt * BnP);
+  // the quadrature stack G [B][NP][121 K] is dead before the signal slabs are written: alias it when it fits
+  const size_t g_elems = (size_t)B * NP * stj_ldg(K);
+  w.G = (g_elems <= (size_t)nt * BnP) ? w.St : c.take<double>(g_elems);
   w.Za = c.take<double>(BnP); w.Zb = c.take<double>(BnP);
   w.Nn = c.take<double>(BnP); w.Nl1 = c.take<double>(BnP);
   w.OM = c.take<double>((size_t)B * (NP + KP) * w.ldP);
@@ -293,7 +305,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   }
   const PanelView pv = view_of(panel);
   const int NP = pfml_padded_n(n_max), P = pv.p + 1, nt = pv.lb + 2, lb = pv.lb;
-  StepWs w = carve_step(workspace, workspace_bytes, B, NP, P, nt, risk == nullptr, tc == nullptr);
+  StepWs w = carve_step(workspace, workspace_bytes, B, NP, P, nt, pv.K, risk == nullptr, tc == nullptr);
   if (w.bytes > workspace_bytes) {
     set_error("pfml_date_steps: workspace too small (%zu < %zu bytes)", workspace_bytes, w.bytes);
     return -3;
@@ -303,23 +315,28 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   const long NN = (long)NP * NP, ldP = w.ldP, nP = (long)NP * ldP, sStack = (long)(NP + KP) * ldP;
   if (status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
 
-  // ---- a3/a4 gathers + a6 standardise -----------------------------------------------------------
+  // ---- a3/a4 gathers ------------------------------------------------------------------------------
   {
     ProfScope ps(T_STD, s);
     PFML_TRY(prep_vectors(pv, B, NP, date_t, sel, n_sel, w.v, s));
-    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, s));
   }
   auto St = [&](int tau) { return w.St + (long)tau * NP * ldP; };   // + b * nt * nP per batch
   const long sSt = (long)nt * nP;
   auto gv = [&](int tau) { return w.v.g + (long)tau * NP; };        // + b * nt * NP per batch
   const long sg = (long)nt * NP;
 
-  // ---- a5 m_tilde -------------------------------------------------------------------------------
+  // ---- a5 m_tilde: m~_0 by quadrature + Woodbury (stieltjes.cu), then the fixed-point inverses -----
   double* mt = nullptr;
   {
     ProfScope ps(T_MFUNC, s);
     PFML_TRY(build_x_factor(pv, B, NP, date_t, sel, n_sel, w.v, w.m.x, w.m.sgr, w.m.yv, s));
-    PFML_TRY(mtilde(B, NP, pv.iterations, w.m, status, s, &mt));
+    PFML_TRY(mt0_stieltjes(B, NP, pv.K, n_sel, w.v, w.Ut, w.Ev, w.G, w.m.mt, status, s));
+    PFML_TRY(fixed_point(B, NP, pv.iterations, w.m, status, s, &mt));
+  }
+  // ---- a6 standardise (after m~: the signal slabs reuse the quadrature stack's memory) -------------
+  {
+    ProfScope ps(T_STD, s);
+    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, s));
   }
   // free n x n buffers after m_tilde: x, sgr, Mdb, Ya, Yb, Wk, T1 and whichever of {mt, Xinv} is not `mt`
   double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
@@ -457,7 +474,7 @@ int pfml_padded_n(int n_max) { return (int)round_up(n_max < 1 ? 1 : n_max, BASE)
 
 size_t pfml_date_steps_workspace_bytes(const pfml_panel_t* panel, int B, int n_max) {
   if (!panel || B <= 0 || n_max <= 0) return 0;
-  StepWs w = carve_step(nullptr, 0, B, pfml_padded_n(n_max), panel->p + 1, panel->lb + 2, true, true);
+  StepWs w = carve_step(nullptr, 0, B, pfml_padded_n(n_max), panel->p + 1, panel->lb + 2, panel->K, true, true);
   return w.bytes;
 }
 
