@@ -5,7 +5,7 @@
 // sm_100a).  Measured issue-bound peak on this pool's B200: 37.05 TFLOP/s (= 148 SMs x 64 FMA/clk x
 // 1.965 GHz); cuBLAS DGEMM 8192^3 reaches 35.4.  One DMMA.8x8x4 needs only two 8-byte operand loads per
 // thread for 8 FMAs and the pipe retires one instruction per 16 clk per SM sub-partition, so operand
-// delivery is cheap: a 128x128x16 CTA tile needs 8 B/clk/SM from L2, far below the 40 B/clk/SM share of
+// delivery is cheap: a 64x64x16 CTA tile needs 16 B/clk/SM from L2, far below the 40 B/clk/SM share of
 // the L2 fabric.  The kernel is therefore a classic multi-stage cp.async (LDGSTS) pipeline into padded
 // shared-memory tiles (conflict-free for the (groupID, threadID_in_group) fragment pattern), with the
 // diagonal scalings / addends / symmetric mirroring the PFML chain needs fused into the epilogue.
@@ -15,7 +15,6 @@ namespace pfml {
 
 namespace {
 
-constexpr int BK = 16;       // k-tile (doubles)
 constexpr int PAD = 4;       // stride == 4 (mod 16) doubles -> the 16 lanes of a half-warp hit 16 distinct bank pairs
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* g, bool pred) {
@@ -43,7 +42,7 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 //   !KIN (k is the row in global):  tile is [BK][ROWS] with row stride ROWS+PAD; element (k,r) = G[(k0+k)*ld + r0+r]
 // Out-of-range elements are zero-filled (cp.async src-size 0).  VEC: 16-byte copies (needs even ld / offsets
 // and 16-byte aligned base), otherwise 8-byte copies.
-template <int ROWS, bool KIN, bool VEC, int NT>
+template <int ROWS, int BK, bool KIN, bool VEC, int NT>
 __device__ __forceinline__ void load_tile(double* s, const double* __restrict__ G, long ld, int r0, int k0, int R, int K, int tid) {
   if (KIN) {
     constexpr int S = BK + PAD;
@@ -90,19 +89,19 @@ __device__ __forceinline__ void load_tile(double* s, const double* __restrict__ 
   }
 }
 
-template <int ROWS, bool KIN>
+template <int ROWS, int BK, bool KIN>
 struct TileSize {
   static constexpr int value = KIN ? ROWS * (BK + PAD) : BK * (ROWS + PAD);
 };
 
-template <int BM, int BN, int WM, int WN, int STAGES, bool AKIN, bool BKIN, bool VEC>
-__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32)
+template <int BM, int BN, int WM, int WN, int BK, int STAGES, int MINB, bool AKIN, bool BKIN, bool VEC>
+__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB)
 gemm_kernel(const GemmP p) {
   constexpr int NWM = BM / WM, NWN = BN / WN;
   constexpr int NT = NWM * NWN * 32;
   constexpr int MT = WM / 8, NTL = WN / 8;            // 8x8 DMMA tiles per warp
-  constexpr int A_SZ = TileSize<BM, AKIN>::value;
-  constexpr int B_SZ = TileSize<BN, BKIN>::value;
+  constexpr int A_SZ = TileSize<BM, BK, AKIN>::value;
+  constexpr int B_SZ = TileSize<BN, BK, BKIN>::value;
   constexpr int SA = AKIN ? BK + PAD : BM + PAD;
   constexpr int SB = BKIN ? BK + PAD : BN + PAD;
 
@@ -126,13 +125,19 @@ gemm_kernel(const GemmP p) {
   for (int i = 0; i < MT; i++)
 #pragma unroll
     for (int j = 0; j < NTL; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+  // 8x8 tiles of this warp that hold at least one valid output (edge CTAs skip the DMMA work of the rest,
+  // e.g. the 9th column tile of P = 1025 holds a single valid column)
+  const int imax = min(MT, max(0, (p.M - m0 - wm0 + 7) >> 3));
+  const int jmax = min(NTL, max(0, (p.N - n0 - wn0 + 7) >> 3));
+  const bool full = (imax == MT) && (jmax == NTL);
+  const bool active = (imax > 0) && (jmax > 0);
 
   const int KT = (p.K + BK - 1) / BK;
 #pragma unroll
   for (int s = 0; s < STAGES - 1; s++) {
     if (s < KT) {
-      load_tile<BM, AKIN, VEC, NT>(As + s * A_SZ, A, p.lda, m0, s * BK, p.M, p.K, tid);
-      load_tile<BN, BKIN, VEC, NT>(Bs + s * B_SZ, B, p.ldb, n0, s * BK, p.N, p.K, tid);
+      load_tile<BM, BK, AKIN, VEC, NT>(As + s * A_SZ, A, p.lda, m0, s * BK, p.M, p.K, tid);
+      load_tile<BN, BK, BKIN, VEC, NT>(Bs + s * B_SZ, B, p.ldb, n0, s * BK, p.N, p.K, tid);
     }
     cp_async_commit();
   }
@@ -144,24 +149,40 @@ gemm_kernel(const GemmP p) {
       int nk = kt + STAGES - 1;
       if (nk < KT) {
         int s = nk % STAGES;
-        load_tile<BM, AKIN, VEC, NT>(As + s * A_SZ, A, p.lda, m0, nk * BK, p.M, p.K, tid);
-        load_tile<BN, BKIN, VEC, NT>(Bs + s * B_SZ, B, p.ldb, n0, nk * BK, p.N, p.K, tid);
+        load_tile<BM, BK, AKIN, VEC, NT>(As + s * A_SZ, A, p.lda, m0, nk * BK, p.M, p.K, tid);
+        load_tile<BN, BK, BKIN, VEC, NT>(Bs + s * B_SZ, B, p.ldb, n0, nk * BK, p.N, p.K, tid);
       }
       cp_async_commit();
     }
     const double* as = As + (kt % STAGES) * A_SZ;
     const double* bs = Bs + (kt % STAGES) * B_SZ;
+    if (full) {
 #pragma unroll
-    for (int kk = 0; kk < BK; kk += 4) {
-      double af[MT], bf[NTL];
+      for (int kk = 0; kk < BK; kk += 4) {
+        double af[MT], bf[NTL];
 #pragma unroll
-      for (int i = 0; i < MT; i++) af[i] = AKIN ? as[(wm0 + 8 * i + g) * SA + kk + t] : as[(kk + t) * SA + wm0 + 8 * i + g];
+        for (int i = 0; i < MT; i++) af[i] = AKIN ? as[(wm0 + 8 * i + g) * SA + kk + t] : as[(kk + t) * SA + wm0 + 8 * i + g];
 #pragma unroll
-      for (int j = 0; j < NTL; j++) bf[j] = BKIN ? bs[(wn0 + 8 * j + g) * SB + kk + t] : bs[(kk + t) * SB + wn0 + 8 * j + g];
+        for (int j = 0; j < NTL; j++) bf[j] = BKIN ? bs[(wn0 + 8 * j + g) * SB + kk + t] : bs[(kk + t) * SB + wn0 + 8 * j + g];
 #pragma unroll
-      for (int i = 0; i < MT; i++)
+        for (int i = 0; i < MT; i++)
 #pragma unroll
-        for (int j = 0; j < NTL; j++) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+          for (int j = 0; j < NTL; j++) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+      }
+    } else if (active) {
+#pragma unroll
+      for (int kk = 0; kk < BK; kk += 4) {
+        double af[MT], bf[NTL];
+#pragma unroll
+        for (int i = 0; i < MT; i++) af[i] = AKIN ? as[(wm0 + 8 * i + g) * SA + kk + t] : as[(kk + t) * SA + wm0 + 8 * i + g];
+#pragma unroll
+        for (int j = 0; j < NTL; j++) bf[j] = BKIN ? bs[(wn0 + 8 * j + g) * SB + kk + t] : bs[(kk + t) * SB + wn0 + 8 * j + g];
+#pragma unroll
+        for (int i = 0; i < MT; i++)
+#pragma unroll
+          for (int j = 0; j < NTL; j++)
+            if (i < imax && j < jmax) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+      }
     }
   }
   cp_async_wait<0>();
@@ -214,11 +235,11 @@ gemm_kernel(const GemmP p) {
   }
 }
 
-template <int BM, int BN, int WM, int WN, int STAGES, bool AKIN, bool BKIN, bool VEC>
+template <int BM, int BN, int WM, int WN, int BK, int STAGES, int MINB, bool AKIN, bool BKIN, bool VEC>
 int launch(const GemmP& p, int batch, cudaStream_t stream) {
   constexpr int NT = (BM / WM) * (BN / WN) * 32;
-  constexpr size_t smem = (size_t)STAGES * (TileSize<BM, AKIN>::value + TileSize<BN, BKIN>::value) * sizeof(double);
-  auto kern = gemm_kernel<BM, BN, WM, WN, STAGES, AKIN, BKIN, VEC>;
+  constexpr size_t smem = (size_t)STAGES * (TileSize<BM, BK, AKIN>::value + TileSize<BN, BK, BKIN>::value) * sizeof(double);
+  auto kern = gemm_kernel<BM, BN, WM, WN, BK, STAGES, MINB, AKIN, BKIN, VEC>;
   static bool configured[64] = {};   // per instantiation and device; the attribute is per-function per-context
   int dev = 0;
   PFML_CUDA_OK(cudaGetDevice(&dev));
@@ -232,12 +253,12 @@ int launch(const GemmP& p, int batch, cudaStream_t stream) {
   return 0;
 }
 
-template <int BM, int BN, int WM, int WN, int STAGES>
+template <int BM, int BN, int WM, int WN, int BK, int STAGES, int MINB>
 int dispatch_layout(const GemmP& p, int batch, cudaStream_t stream, bool vec) {
 #define PFML_GEMM_CASE(AK, BK_)                                                                 \
   if (p.a_kinner == AK && p.b_kinner == BK_) {                                                  \
-    return vec ? launch<BM, BN, WM, WN, STAGES, AK, BK_, true>(p, batch, stream)                \
-               : launch<BM, BN, WM, WN, STAGES, AK, BK_, false>(p, batch, stream);              \
+    return vec ? launch<BM, BN, WM, WN, BK, STAGES, MINB, AK, BK_, true>(p, batch, stream)      \
+               : launch<BM, BN, WM, WN, BK, STAGES, MINB, AK, BK_, false>(p, batch, stream);    \
   }
   PFML_GEMM_CASE(true, false)
   PFML_GEMM_CASE(false, false)
@@ -272,10 +293,11 @@ int gemm(const GemmP& p, int batch, cudaStream_t stream) {
   // the (even) leading dimension, and that lane's output column is never stored.
   prof_begin(-1, stream);
   int rc;
-  if (p.M <= 64 || p.N <= 64 || (long)p.M * p.N <= 128L * 128L)
-    rc = dispatch_layout<64, 64, 32, 32, 3>(p, batch, stream, vec);
-  else
-    rc = dispatch_layout<128, 128, 64, 32, 3>(p, batch, stream, vec);
+  // One configuration for every shape: 64x64x16 CTA tile, 4 warps x (32x32), 3 cp.async stages, 3 CTAs per SM.
+  // Measured on B200 for the Horner step (148 x [512 x 1025 x 512]): 30.5 TFLOP/s, against 24.2 for
+  // 128x128 / 8 warps / 1 CTA per SM and 27.9 for 128x64 / 2 CTAs per SM -- independent CTAs hide each other's
+  // per-k-tile barrier, which a single big CTA cannot (profiles/r01_gemm_tile_sweep.md).
+  rc = dispatch_layout<64, 64, 32, 32, 16, 3, 3>(p, batch, stream, vec);
   prof_end(-1, stream, gemm_flops(p, batch), 0.0);
   return rc;
 }
