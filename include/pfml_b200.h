@@ -79,6 +79,25 @@ int pfml_mfunc_batched(int B, int n, const double* sigma_gam, const double* lam,
                        double mu, double gam, int iterations, double* m_out, int* status, void* workspace,
                        size_t workspace_bytes, void* stream);
 
+/* a11 -- expanding-window sums of PFML_Search_Coef.py:37-46, :77-88, :112-121.  bucket[b] (device int32) is the
+ * window of date b (0 = burn-in, k = k-th hp year, -1 = unused); r_sum [n_buckets][P] and d_sum [n_buckets][P][P]
+ * are ACCUMULATED into (zero them first; partial sums of different ranks are then added with an all-reduce).
+ * Sums run over dates in order, one thread per element: the reference's left-to-right reduce().
+ * pfml_bucket_cumsum turns bucket sums into the running sums the year loop keeps (:117, :121). */
+int pfml_bucket_accumulate(const double* r_tilde, const double* denom, const int* bucket, int B, int P, int n_buckets,
+                           double* r_sum, double* d_sum, void* stream);
+int pfml_bucket_cumsum(double* r_sum, double* d_sum, int P, int n_buckets, void* stream);
+
+/* a12/a13 -- the ridge grid of PFML_Search_Coef.py:125-135: for every year y < Y, every p in p_vec (HOST array,
+ * even, <= p_max) and every lambda in l_vec (device): beta = solve(D_sub / n_y + lambda I, r_sub / n_y), where
+ * D = d_cum[y], r = r_cum[y], n_y = n_cum[y] (device, number of dates summed) and `sub` is the index set of
+ * pfml_feat_fun(p) (General_functions.py:837-844) inside the p_max layout.  beta is packed per p:
+ * [p][Y][n_l][p+1]; status [n_p][Y][n_l] (may be NULL). */
+size_t pfml_ridge_grid_workspace_bytes(int Y, int p_max, int n_l);
+int pfml_ridge_grid(const double* r_cum, const double* d_cum, const double* n_cum, int Y, int p_max, const int* p_vec_host,
+                    int n_p, const double* l_vec, int n_l, double* beta, int* status, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
 /* General batched FP64 GEMM on the DMMA pipe, D = alpha * op(A) op(B) + beta * D0 (the reference's `@`):
  * trans_a/trans_b = 0: stored [M][K] / [K][N]; 1: stored transposed.  Batch strides in elements. */
 int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alpha, const double* A, long lda, long sA,

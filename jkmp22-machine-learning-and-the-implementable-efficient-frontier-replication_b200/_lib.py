@@ -59,6 +59,12 @@ SIGNATURES = {
     "pfml_mfunc_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "pfml_mfunc_batched": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double,
                                      C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "pfml_bucket_accumulate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.c_void_p]),
+    "pfml_bucket_cumsum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "pfml_ridge_grid_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "pfml_ridge_grid": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                  C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "pfml_dgemm_batched": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_void_p, C.c_long, C.c_long, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_int, C.c_void_p]),

@@ -168,6 +168,12 @@ static int inv_rec(const InvCtx& c, int off, int size) {
 
 static int inverse(const InvCtx& c) { return inv_rec(c, 0, c.NP); }
 
+// symmetric positive definite batch inverse for other translation units (ridge.cu)
+int spd_inverse(int B, int NP, double* Wk, double* X, double* T1, int* status, cudaStream_t s) {
+  InvCtx c{B, NP, Wk, X, T1, status, s, true};
+  return inverse(c);
+}
+
 // ------------------------------------------------------------------------------------------------
 // m_tilde: General_functions.py:955-960 given x, sigma_gr, y.  Result pointer returned in *mt_out
 // (one of mt / Xinv, they ping-pong).
