@@ -333,120 +333,118 @@ __global__ void m_from_mtilde_kernel(int n, int NP, const double* __restrict__ m
 }
 
 // ------------------------------------------------------------------------------------------------
-// Gauss-Jordan inverse of one NB x NB diagonal block per CTA (NB = 64 or 128), matrix held in REGISTERS:
-// thread (ti, tj) owns the 4x4 tile rows 4ti.., cols 4tj..; per pivot step the owners of the pivot row and of
-// column k publish them through double-buffered shared memory, everybody updates its 16 elements.
+// Gauss-Jordan inverse of one NB x NB diagonal block per CTA (NB = 64 or 128), matrix held in REGISTERS.
+// 256 threads in a 16 x 16 grid with a CYCLIC distribution: thread (ti, tj) owns rows ti + 16 r and columns
+// tj + 16 c (r, c < TS = NB / 16).  Column k = 16 cb + kk then lives in register column cb of the threads with
+// tj == kk, so an outer loop over cb unrolled at compile time makes every register index static (no selects,
+// no local memory).  Per pivot step the owners publish column k and the pivot row through double-buffered
+// shared memory and every thread applies the rank-1 update to its tile (TS^2 DFMAs).
 // PIVOT = false (SPD blocks of m_tilde's fixed point): pivot k is row k, one barrier per step.
-// PIVOT = true  (general blocks): implicit partial pivoting -- the pivot row is the unused row with the largest
-// |a[r][k]|, rows are never moved, the permutation is undone when the result is written
-// (Ainv[k][p_c] = stored[p_k][c]).  Threads are numbered tid = tj * (NB/4) + ti so that the owners of a column
-// sit in one warp (NB = 128) / half-warp (NB = 64) and the pivot search is a shuffle reduction.
+// PIVOT = true  (general blocks): implicit partial pivoting -- every warp finds the unused row with the largest
+// |a[r][k]| from the published column, rows are never moved and the permutation is undone on output
+// (Ainv[k][p_c] = stored[p_k][c]).
 // ------------------------------------------------------------------------------------------------
 template <int NB, bool PIVOT>
-__global__ void __launch_bounds__((NB / 4) * (NB / 4))
+__global__ void __launch_bounds__(256)
 gj_inverse_kernel(int NP, const double* __restrict__ src, double* __restrict__ dst, int off, int* __restrict__ status) {
-  constexpr int TD = NB / 4;               // threads per tile dimension
-  __shared__ double prow[2][NB], pcol[2][NB];
+  constexpr int TS = NB / 16;
+  __shared__ double prow[2][NB];
+  __shared__ double pcol[2][NB];
   __shared__ int s_piv[NB];                // pivot row of step k
   __shared__ int s_pinv[NB];               // step at which row r was the pivot
+  __shared__ int s_used[NB];
   __shared__ int bad;
   const int b = blockIdx.x, tid = threadIdx.x;
-  const int ti = tid % TD, tj = tid / TD;
+  const int ti = tid >> 4, tj = tid & 15, lane = tid & 31;
   const double* S = src + (long)b * NP * NP + (long)off * NP + off;
   double* Dp = dst + (long)b * NP * NP + (long)off * NP + off;
   if (tid == 0) bad = 0;
-  double a[4][4];
+  if (PIVOT && tid < NB) s_used[tid] = 0;
+  double a[TS][TS];
 #pragma unroll
-  for (int r = 0; r < 4; r++) {
-    const double2* s2 = reinterpret_cast<const double2*>(S + (long)(4 * ti + r) * NP + 4 * tj);
-    double2 v0 = s2[0], v1 = s2[1];
-    a[r][0] = v0.x; a[r][1] = v0.y; a[r][2] = v1.x; a[r][3] = v1.y;
-  }
-  unsigned used = 0;                       // bit r: my row 4ti+r has been a pivot row
-  for (int k = 0; k < NB; k++) {
-    const int buf = k & 1;
-    const int kj = k >> 2, kc = k & 3;
-    int p = k;
-    if (PIVOT) {
-      if (tj == kj) {                      // owners of column k: one (half-)warp
+  for (int r = 0; r < TS; r++)
+#pragma unroll
+    for (int c = 0; c < TS; c++) a[r][c] = S[(long)(ti + 16 * r) * NP + tj + 16 * c];
+  if (PIVOT) __syncthreads();
+#pragma unroll
+  for (int cb = 0; cb < TS; cb++) {
+#pragma unroll 1
+    for (int kk = 0; kk < 16; kk++) {
+      const int k = 16 * cb + kk, buf = k & 1;
+      if (tj == kk) {                      // owners of column k publish it and clear it in their tile
+#pragma unroll
+        for (int r = 0; r < TS; r++) {
+          pcol[buf][ti + 16 * r] = a[r][cb];
+          a[r][cb] = 0.0;
+        }
+      }
+      int p = k;
+      if (PIVOT) {
+        __syncthreads();
         double best = -1.0;
         int bi = -1;
 #pragma unroll
-        for (int r = 0; r < 4; r++) {
-          double akc = a[r][0];                      // static register indexing only (no local-memory array)
-#pragma unroll
-          for (int c = 1; c < 4; c++) akc = (c == kc) ? a[r][c] : akc;
-          const double v = fabs(akc);                // NaN never wins a comparison: an all-NaN column is flagged
-          if (!((used >> r) & 1u) && v > best) { best = v; bi = 4 * ti + r; }
+        for (int m = 0; m < NB / 32; m++) {
+          const int i = lane + 32 * m;
+          const double v = fabs(pcol[buf][i]);       // NaN never wins a comparison: an all-NaN column is flagged
+          if (!s_used[i] && v > best) { best = v; bi = i; }
         }
-        const unsigned mask = (TD == 32) ? 0xffffffffu : (0xffffu << (tid & 16));
 #pragma unroll
-        for (int o = TD / 2; o > 0; o >>= 1) {
-          const double ob = __shfl_xor_sync(mask, best, o, TD);
-          const int oi = __shfl_xor_sync(mask, bi, o, TD);
+        for (int o = 16; o > 0; o >>= 1) {
+          const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+          const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
           if (ob > best || (ob == best && oi >= 0 && (bi < 0 || oi < bi))) { best = ob; bi = oi; }
         }
-        if (ti == 0) {
-          s_piv[k] = bi < 0 ? k : bi;
+        p = bi < 0 ? k : bi;                         // identical in every warp
+        if (tid == 0) {
+          s_piv[k] = p; s_pinv[p] = k;
           if (!(best > 0.0) || !isfinite(best)) bad = 1;
         }
       }
+      const int rhi = PIVOT ? (p >> 4) : cb, rlo = PIVOT ? (p & 15) : kk;
+      if (ti == rlo) {                     // owners of the pivot row publish it
+#pragma unroll
+        for (int r = 0; r < TS; r++)
+          if (r == rhi) {
+#pragma unroll
+            for (int c = 0; c < TS; c++) prow[buf][tj + 16 * c] = a[r][c];
+          }
+      }
       __syncthreads();
-      p = s_piv[k];
-    } else if (tid == 0) {
-      s_piv[k] = k;
-    }
-    const int pi = p >> 2, pr = p & 3;
-    if (ti == pi) {                        // owners of the pivot row publish it
+      if (PIVOT && tid == 0) s_used[p] = 1;          // read again only after the next step's first barrier
+      const double pv = pcol[buf][p];
+      if (!PIVOT && tid == 0 && (!(fabs(pv) > 0.0) || !isfinite(pv))) bad = 1;
+      const double ipv = 1.0 / pv;
+      double q[TS], f[TS];
 #pragma unroll
-      for (int r = 0; r < 4; r++)
-        if (r == pr) {
+      for (int c = 0; c < TS; c++) q[c] = prow[buf][tj + 16 * c] * ipv;
+      if (tj == kk) q[cb] = ipv;
 #pragma unroll
-          for (int c = 0; c < 4; c++) prow[buf][4 * tj + c] = a[r][c];
-        }
-      used |= 1u << pr;
-      if (tj == 0) s_pinv[p] = k;
-    }
-    if (tj == kj) {                        // owners of column k publish it
+      for (int r = 0; r < TS; r++) f[r] = pcol[buf][ti + 16 * r];
 #pragma unroll
-      for (int r = 0; r < 4; r++) {
-        double akc = a[r][0];
+      for (int r = 0; r < TS; r++)
 #pragma unroll
-        for (int c = 1; c < 4; c++) akc = (c == kc) ? a[r][c] : akc;
-        pcol[buf][4 * ti + r] = akc;
+        for (int c = 0; c < TS; c++) a[r][c] -= f[r] * q[c];
+      if (ti == rlo) {                     // the pivot row itself becomes q
+#pragma unroll
+        for (int r = 0; r < TS; r++)
+          if (r == rhi) {
+#pragma unroll
+            for (int c = 0; c < TS; c++) a[r][c] = q[c];
+          }
       }
+      // double-buffered prow/pcol: the next step writes the other buffer, and its barrier orders this step's reads
     }
-    __syncthreads();
-    const double pv = prow[buf][k];
-    if (!PIVOT && tid == 0 && (!(fabs(pv) > 0.0) || !isfinite(pv))) bad = 1;
-    const double ipv = 1.0 / pv;
-    double q[4], f[4];
-#pragma unroll
-    for (int c = 0; c < 4; c++) q[c] = (4 * tj + c == k) ? ipv : prow[buf][4 * tj + c] * ipv;
-#pragma unroll
-    for (int r = 0; r < 4; r++) f[r] = pcol[buf][4 * ti + r];
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-      const bool is_p = (4 * ti + r == p);
-#pragma unroll
-      for (int c = 0; c < 4; c++) {
-        const double old = (4 * tj + c == k) ? 0.0 : a[r][c];
-        a[r][c] = is_p ? q[c] : old - f[r] * q[c];
-      }
-    }
-    // double-buffered prow/pcol: the next step writes the other buffer, and its barrier orders this step's reads
   }
   __syncthreads();
 #pragma unroll
-  for (int r = 0; r < 4; r++) {
-    const int orow = PIVOT ? s_pinv[4 * ti + r] : 4 * ti + r;
-    if (PIVOT) {
+  for (int r = 0; r < TS; r++) {
+    const int row = ti + 16 * r;
+    const int orow = PIVOT ? s_pinv[row] : row;
 #pragma unroll
-      for (int c = 0; c < 4; c++) Dp[(long)orow * NP + s_piv[4 * tj + c]] = a[r][c];
-    } else {
-      double2* d2 = reinterpret_cast<double2*>(Dp + (long)orow * NP + 4 * tj);
-      d2[0] = make_double2(a[r][0], a[r][1]);
-      d2[1] = make_double2(a[r][2], a[r][3]);
+    for (int c = 0; c < TS; c++) {
+      const int col = tj + 16 * c;
+      Dp[(long)orow * NP + (PIVOT ? s_piv[col] : col)] = a[r][c];
     }
   }
   if (tid == 0 && bad && status) atomicOr(status + b, 1);
@@ -640,8 +638,8 @@ int base_inverse(int B, int NP, const double* src, double* dst, int off, int siz
     if (spd) gj_inverse_kernel<64, false><<<B, 256, 0, s>>>(NP, src, dst, off, status);
     else gj_inverse_kernel<64, true><<<B, 256, 0, s>>>(NP, src, dst, off, status);
   } else if (size == 128) {
-    if (spd) gj_inverse_kernel<128, false><<<B, 1024, 0, s>>>(NP, src, dst, off, status);
-    else gj_inverse_kernel<128, true><<<B, 1024, 0, s>>>(NP, src, dst, off, status);
+    if (spd) gj_inverse_kernel<128, false><<<B, 256, 0, s>>>(NP, src, dst, off, status);
+    else gj_inverse_kernel<128, true><<<B, 256, 0, s>>>(NP, src, dst, off, status);
   } else {
     set_error("base_inverse: unsupported block size %d", size);
     return -2;

@@ -71,44 +71,55 @@ stj_prep_kernel(int NP, int K, const int* __restrict__ nsel, BatchVecs v, double
   for (int i = tid; i < NP; i += blockDim.x) Ev[(long)b * NP + i] = (i < n) ? v.dvl[(long)b * NP + i] * iw : 1.0;
 }
 
-// One CTA per (node j, date b): T_j = I + U~' D_j U~, Cholesky, L_j^-1, G_j = sqrt(w_j) D_j U~ L_j^-T.
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+// One CTA (4 warps) per (node j, date b):
+//   T_j = I + U~' D_j U~          32 x 32 x n contraction on the DMMA pipe (warp w owns rows 8w..8w+7 of T)
+//   T_j = L L', L^-1               one warp, shared memory
+//   G_j = (D_j U~) (sqrt(w_j) L^-T)  n x 32 x 32 on the DMMA pipe, written straight to the stack G
+// U~ is streamed through shared memory in chunks of 64 rows (stride 36 doubles: conflict-free for both the
+// k-outer fragment pattern of the first product and the k-inner pattern of the second).
 __global__ void __launch_bounds__(128)
 stj_node_kernel(int NP, int K, int KQ, long ldG, const double* __restrict__ Ut, const double* __restrict__ Ev, double* __restrict__ G) {
-  constexpr int CH = 64;
-  __shared__ double T[KP][KP + 1];
-  __shared__ double Li[KP][KP + 1];
-  __shared__ double Uc[CH][KP + 1];
+  constexpr int CH = 64, S = KP + 4;
+  __shared__ double T[KP][S];
+  __shared__ double Li[KP][S];
+  __shared__ double Uc[CH][S];
   __shared__ double dc[CH];
   const int j = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   double u, w;
   sq_node(j, u, w);
   const double* U = Ut + (long)b * NP * KP;
   const double* E = Ev + (long)b * NP;
   // ---- T = I + sum_i d_i u_i u_i' -----------------------------------------------------------------
-  double acc[8];
+  double acc[4][2];
 #pragma unroll
-  for (int q = 0; q < 8; q++) acc[q] = 0.0;
+  for (int q = 0; q < 4; q++) acc[q][0] = acc[q][1] = 0.0;
   for (int i0 = 0; i0 < NP; i0 += CH) {
     __syncthreads();
     for (int e = tid; e < CH * KP; e += 128) Uc[e / KP][e % KP] = U[(long)(i0 + e / KP) * KP + e % KP];
     if (tid < CH) dc[tid] = 1.0 / (E[i0 + tid] + u);
     __syncthreads();
+#pragma unroll 4
+    for (int k0 = 0; k0 < CH; k0 += 4) {
+      const double af = Uc[k0 + t][8 * warp + g] * dc[k0 + t];
 #pragma unroll
-    for (int q = 0; q < 8; q++) {
-      const int e = tid + 128 * q, a = e / KP, c = e % KP;
-      if (a < K && c <= a) {
-        double s = 0.0;
-#pragma unroll 8
-        for (int i = 0; i < CH; i++) s += dc[i] * Uc[i][a] * Uc[i][c];
-        acc[q] += s;
-      }
+      for (int q = 0; q < 4; q++) dmma884(acc[q][0], acc[q][1], af, Uc[k0 + t][8 * q + g]);
     }
   }
+  __syncthreads();
 #pragma unroll
-  for (int q = 0; q < 8; q++) {
-    const int e = tid + 128 * q, a = e / KP, c = e % KP;
-    T[a][c] = acc[q] + (a == c ? 1.0 : 0.0);
-    Li[a][c] = 0.0;
+  for (int q = 0; q < 4; q++) {
+    const int r = 8 * warp + g, c = 8 * q + 2 * t;
+    T[r][c] = acc[q][0] + (r == c ? 1.0 : 0.0);
+    T[r][c + 1] = acc[q][1] + (r == c + 1 ? 1.0 : 0.0);
+    Li[r][c] = 0.0;
+    Li[r][c + 1] = 0.0;
   }
   __syncthreads();
   // ---- Cholesky T = L L' (lower, in place) and L^-1, one warp -------------------------------------
@@ -135,20 +146,39 @@ stj_node_kernel(int NP, int K, int KQ, long ldG, const double* __restrict__ Ut, 
     }
   }
   __syncthreads();
-  // ---- G_j rows: sqrt(w) d_i L^-1 u_i -------------------------------------------------------------
+  // ---- G_j = (D_j U~) (sqrt(w) L^-T): B fragments (k = a, n = c) = sqrt(w) Li[c][a], kept in registers ----
   const double sw = sqrt(w);
+  double bf[8][4];
+#pragma unroll
+  for (int kk = 0; kk < 8; kk++)
+#pragma unroll
+    for (int q = 0; q < 4; q++) bf[kk][q] = sw * Li[8 * q + g][4 * kk + t];
   double* Gj = G + (long)b * NP * ldG + (long)j * KQ;
-  for (int i = tid; i < NP; i += 128) {
-    double uu[KP];
+  for (int i0 = 0; i0 < NP; i0 += CH) {
+    __syncthreads();
+    for (int e = tid; e < CH * KP; e += 128) Uc[e / KP][e % KP] = U[(long)(i0 + e / KP) * KP + e % KP];
+    if (tid < CH) dc[tid] = 1.0 / (E[i0 + tid] + u);
+    __syncthreads();
 #pragma unroll
-    for (int a = 0; a < KP; a++) uu[a] = U[(long)i * KP + a];
-    const double f = sw / (E[i] + u);
+    for (int mi = 0; mi < 2; mi++) {
+      const int r = 16 * warp + 8 * mi + g;
+      const double dr = dc[r];
+      double c4[4][2];
 #pragma unroll
-    for (int c = 0; c < KP; c++) {
-      double z = 0.0;
+      for (int q = 0; q < 4; q++) c4[q][0] = c4[q][1] = 0.0;
 #pragma unroll
-      for (int a = 0; a <= c; a++) z += Li[c][a] * uu[a];
-      if (c < KQ) Gj[(long)i * ldG + c] = f * z;
+      for (int kk = 0; kk < 8; kk++) {
+        const double af = Uc[r][4 * kk + t] * dr;
+#pragma unroll
+        for (int q = 0; q < 4; q++) dmma884(c4[q][0], c4[q][1], af, bf[kk][q]);
+      }
+      double* row = Gj + (long)(i0 + r) * ldG;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int c = 8 * q + 2 * t;
+        if (c + 1 < KQ) *reinterpret_cast<double2*>(row + c) = make_double2(c4[q][0], c4[q][1]);
+        else if (c < KQ) row[c] = c4[q][0];
+      }
     }
   }
 }
