@@ -93,6 +93,16 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1; the CPU arm must use every host core (BLAS threads = os.cpu_count())."""
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=os.cpu_count())
+    except Exception:
+        pass
+    return os.cpu_count()
+
+
 def make_bench_panel(syn, B, seed):
     return syn.make_panel(N=N_STOCKS, T=syn.LB + 2 + B, p=P_FEAT, seed=seed, g=float(np.exp(-3.0)))
 
@@ -100,6 +110,7 @@ def make_bench_panel(syn, B, seed):
 def cpu_dates_per_sec(syn, budget_s=20.0, max_dates=8, seed=101):
     """Oracle (numpy port of the reference algorithm, all host BLAS threads) on a bounded sample of the workload."""
     import pfml_oracle as O
+    use_all_host_threads()
     panel = make_bench_panel(syn, max_dates, seed)
     T, N, F = panel.feats.shape
     rff_x = O.rff(panel.feats.reshape(T * N, F), panel.W).reshape(T, N, -1)      # a1, excluded like on the GPU side
@@ -120,7 +131,7 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     syn = importlib.import_module(PKG + ".synthetic")
-    cores = os.cpu_count()
+    cores = use_all_host_threads()
     per_step = 2
     import pfml_oracle as O
     panel = make_bench_panel(syn, per_step, 101)

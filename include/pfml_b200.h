@@ -98,6 +98,25 @@ int pfml_ridge_grid(const double* r_cum, const double* d_cum, const double* n_cu
                     int n_p, const double* l_vec, int n_l, double* beta, int* status, void* workspace,
                     size_t workspace_bytes, void* stream);
 
+/* a15 -- daily cross-sectional OLS of "Estimate Covariance Matrix.py":214-241.  Rows are sorted by day; day d owns
+ * rows [day_ptr[d], day_ptr[d+1]) of X [rows][K] and y [rows] (day_ptr: device int64 [n_days+1]).  Outputs
+ * coef [n_days][K] (= fct_ret) and the residuals [rows].  A factor whose column is empty that day (exactly
+ * singular X'X, where the reference falls back to pinv, :226-229) gets coefficient 0 and status bit 0. */
+int pfml_xs_ols_daily(const double* X, const double* y, const long* day_ptr, int n_days, int K, double* coef,
+                      double* resid, int* status, void* stream);
+
+/* a16 -- EWMA factor covariance per calc date, "Estimate Covariance Matrix.py":297-335 with weighted_cor_wt /
+ * weighted_cov_wt of General_functions.py:745-835: window = the last min(obs, end_idx[c]+1) rows of fct_ret
+ * [D][K] ending at row end_idx[c]; weights = the tails of w_cor / w_var [obs] (:280-282);
+ * cov_out[c] = scale * sd_var cor sd_var (scale = 21 for the monthly conversion at :476). */
+int pfml_wcov_wcor(const double* fct_ret, const int* end_idx, int n_calc, int K, int obs, const double* w_cor,
+                   const double* w_var, double scale, double* cov_out, void* stream);
+
+/* a17 -- ewma_vol(x, lam, start) of "Estimate Covariance Matrix.py":345-386 for n_series residual series stored
+ * back to back (series s = x[series_ptr[s] .. series_ptr[s+1]), device int64 pointers): NaN for the first `start`
+ * entries, var_start = sum x^2 / (count - 1), var_i = lam var_{i-1} + (1 - lam) x_{i-1}^2 (NaN carries). */
+int pfml_ewma_vol(const double* x, const long* series_ptr, int n_series, double lam, int start, double* vol, void* stream);
+
 /* General batched FP64 GEMM on the DMMA pipe, D = alpha * op(A) op(B) + beta * D0 (the reference's `@`):
  * trans_a/trans_b = 0: stored [M][K] / [K][N]; 1: stored transposed.  Batch strides in elements. */
 int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alpha, const double* A, long lda, long sA,

@@ -65,6 +65,11 @@ SIGNATURES = {
     "pfml_ridge_grid_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "pfml_ridge_grid": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
                                   C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "pfml_xs_ols_daily": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
+    "pfml_wcov_wcor": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_double,
+                                 C.c_void_p, C.c_void_p]),
+    "pfml_ewma_vol": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),
     "pfml_dgemm_batched": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_void_p, C.c_long, C.c_long, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_int, C.c_void_p]),
