@@ -149,3 +149,32 @@ def denom_sum_fun(train):
     _, d_sum = bucket_sums(rt, dn, np.zeros(B, dtype=np.int32), 1)
     torch.cuda.synchronize()
     return d_sum[0].cpu().numpy()
+
+
+def run(path, settings=None, device="cuda:0"):
+    """PFML_Search_Coef.py: reads Data/pfml_input_{g}.pkl, writes Data/coef_dict_{g}.pkl (:60-143), same schema
+    ``{g: {year: {p: {lambda_index: Series}}}}``."""
+    import os
+    import pickle
+
+    import pandas as pd
+
+    from . import general_functions as GF
+    settings, _pf = settings or GF.get_settings()
+    hp_years = np.arange(settings["pf"]["dates"]["start_year"], settings["pf"]["dates"]["end_yr"] + 1)
+    p_vec, l_vec = settings["pf_ml"]["p_vec"], settings["pf_ml"]["l_vec"]
+    out = {}
+    for g_index, _g in enumerate(settings["pf_ml"]["g_vec"]):
+        with open(os.path.join(path, "Data", f"pfml_input_{g_index}.pkl"), "rb") as f:
+            reals = pickle.load(f)[g_index]["reals"]
+        d_all = sorted(reals.keys())
+        r_t = np.stack([reals[d]["r_tilde"].to_numpy() for d in d_all])
+        den = np.stack([reals[d]["denom"].to_numpy() for d in d_all])
+        me = np.array([np.datetime64(pd.Timestamp(d).date()) for d in d_all])
+        coef = search_coef(r_t, den, me, hp_years, p_vec, l_vec, device=device)
+        coef_dict = {int(y): {int(p): {j: pd.Series(coef[int(y)][int(p)][j], index=pfml_feat_fun(int(p))) for j in range(len(l_vec))}
+                              for p in p_vec} for y in hp_years}
+        with open(os.path.join(path, "Data", f"coef_dict_{g_index}.pkl"), "wb") as f:
+            pickle.dump({g_index: coef_dict}, f)
+        out[g_index] = coef_dict
+    return out

@@ -39,45 +39,12 @@ def _import_general_functions():
 
 
 def write_reference_inputs(panel, path):
-    """Write Factors_processed, FF_RF_monthly.csv, wealth_processed.csv, Barra_Cov.pkl, rff_w.csv."""
+    """Write Factors_processed, FF_RF_monthly.csv, wealth_processed.csv, Barra_Cov.pkl, rff_w.csv (the writer lives
+    in the package so that the GPU tests can use it without the reference tree)."""
+    import importlib
     GF = _import_general_functions()
-    feats = GF.get_features(True)
-    data = os.path.join(path, "Data")
-    os.makedirs(data, exist_ok=True)
-    T, N, F = panel.feats.shape
-    assert F == len(feats)
-    me = pd.to_datetime(panel.month_ends)
-    rows = {
-        "id": np.tile(panel.ids, T),
-        "eom": np.repeat(me.strftime("%Y-%m-%d 00:00:00").values, N),
-        "sic": 0, "ff49": 0, "size_grp": "large", "me": 1.0, "crsp_exchcd": 1, "dolvol": 1.0,
-        "lambda": panel.lam.reshape(-1), "rvol_m": 0.0, "tr_ld0": panel.tr_ld0.reshape(-1),
-        "eom_ret": np.repeat((me + pd.offsets.MonthEnd(1)).strftime("%Y-%m-%d 00:00:00").values, N),
-        "ret_ld1": panel.ret_ld1.reshape(-1), "tr_ld1": 0.0, "mu_ld0": panel.mu_ld0.reshape(-1),
-        "ff12": "1", "valid": panel.valid.reshape(-1).astype(int),
-    }
-    df = pd.DataFrame(rows)
-    df = pd.concat([df, pd.DataFrame(panel.feats.reshape(T * N, F), columns=feats)], axis=1)
-    con = sqlite3.connect(os.path.join(data, "JKP_US_SP500.db"))
-    df.to_sql("Factors_processed", con, if_exists="replace", index=False)
-    con.close()
-    pd.DataFrame({"yyyymm": me.strftime("%Y%m").astype(int), "RF": panel.rf * 100.0}).to_csv(
-        os.path.join(data, "FF_RF_monthly.csv"), index=False)
-    pd.DataFrame({"eom": me, "wealth": panel.wealth, "mu_ld1": 0.0}).to_csv(
-        os.path.join(data, "wealth_processed.csv"), index=False)
-    names = [f"f{k}" for k in range(panel.fct_cov.shape[1])]
-    barra = {}
-    for t in range(T):
-        has = panel.barra_has[t]
-        ids = panel.ids[has].astype(int)
-        barra[me[t]] = {
-            "fct_load": pd.DataFrame(panel.fct_load[t][has], index=ids, columns=names),
-            "fct_cov": pd.DataFrame(panel.fct_cov[t], index=names, columns=names),
-            "ivol_vec": pd.Series(panel.ivol[t][has], index=ids),
-        }
-    with open(os.path.join(data, "Barra_Cov.pkl"), "wb") as f:
-        pickle.dump(barra, f)
-    pd.DataFrame(panel.W).to_csv(os.path.join(data, "rff_w.csv"))      # index column -> 'Unnamed: 0'
+    syn = importlib.import_module("jkmp22-machine-learning-and-the-implementable-efficient-frontier-replication_b200.synthetic")
+    syn.write_reference_artefacts(panel, path, GF.get_features(True))
 
 
 def _settings_wrapper(GF, panel, p_vec, l_vec, start_year, end_yr, n_g=1):

@@ -1,0 +1,70 @@
+"""GPU: the script-level drop-ins (path contract of Main.py:21-22) against the outputs of the reference scripts.
+
+The artefacts under Data/ are written from the golden panel with the same writer the reference run used; the
+drop-ins read them, compute on the GPU and write pfml_input_0.pkl / coef_dict_0.pkl, which must match what the
+exec'd PFML_Input_Data.py / PFML_Search_Coef.py wrote (tests/golden/pfml_ref_small.npz) to 1e-8."""
+import os
+import pickle
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from conftest import GOLD, panel_from_golden, pkg, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+def test_pfml_input_data_and_search_coef_scripts(tmp_path, syn):
+    z = np.load(os.path.join(GOLD, "pfml_ref_small.npz"))
+    panel = panel_from_golden(z, syn)
+    path = str(tmp_path) + "/"
+    syn.write_reference_artefacts(panel, path)
+    GF = pkg("general_functions")
+    settings, pf_set = GF.get_settings()
+    settings["split"]["test_end"] = pd.Timestamp(panel.month_ends[-1])
+    settings["pf"]["dates"].update(start_year=2013, end_yr=2014)
+    settings["pf_ml"].update(g_vec=[panel.meta["g"]], p_vec=[int(p) for p in z["p_vec"]], l_vec=[float(l) for l in z["l_vec"]])
+    out = pkg("pfml_input_data").run(path, (settings, pf_set))[0]
+    dates = sorted(out["reals"].keys())
+    assert len(dates) == len(z["hot"])
+    assert [pd.Timestamp(panel.month_ends[t]) for t in z["hot"]] == dates
+    feat_all = GF.pfml_feat_fun(panel.p)
+    for k, d in enumerate(dates):
+        r = out["reals"][d]
+        assert list(r["r_tilde"].index) == feat_all and list(r["denom"].columns) == feat_all
+        for name in ("r_tilde", "denom", "risk", "tc"):
+            assert relerr(r[name].to_numpy(), z[name][k]) < 1e-8, (name, k)
+        n = int(z["n_d"][k])
+        s = out["signal_t"][d]
+        assert s.shape == (n, panel.p + 1) and list(s.index) == list(panel.ids[panel.valid[z["hot"][k]]])
+        assert relerr(s.to_numpy(), z["signal_t"][k, :n]) < 1e-8
+    with open(os.path.join(path, "Data", "pfml_input_0.pkl"), "rb") as f:
+        assert set(pickle.load(f)[0].keys()) == {"reals", "signal_t", "rff_w"}
+    coef = pkg("pfml_search_coef").run(path, (settings, pf_set))[0]
+    for y in z["years"]:
+        for p in z["p_vec"]:
+            ref = z[f"coef_{y}_{p}"]
+            for j, l in enumerate(z["l_vec"]):
+                s = coef[int(y)][int(p)][j]
+                assert list(s.index) == GF.pfml_feat_fun(int(p))
+                if l > 0:
+                    assert relerr(s.to_numpy(), ref[j]) < 1e-8, (y, p, l)
+
+
+def test_function_mirrors(syn):
+    GF = pkg("general_functions")
+    f = np.load(os.path.join(GOLD, "funcs_ref.npz"))
+    m = GF.m_func(float(f["m_w"]), float(f["m_mu"]), float(f["m_rf"]), f["m_sigma"] * 10.0, 10.0, np.diag(f["m_lam"]), 10)
+    assert relerr(m, f["m_ref"]) < 1e-8
+    pn = syn.make_panel(N=40, T=14, p=8, seed=5)
+    x = {"fct_load": pd.DataFrame(pn.fct_load[13], index=pn.ids), "fct_cov": pd.DataFrame(pn.fct_cov[13]),
+         "ivol_vec": pd.Series(pn.ivol[13], index=pn.ids)}
+    ids = pn.ids[::3]
+    sig = GF.create_cov(x, ids)
+    L = x["fct_load"].loc[ids].to_numpy()
+    assert relerr(sig.to_numpy(), L @ pn.fct_cov[13] @ L.T + np.diag(pn.ivol[13][::3])) < 1e-13
+    assert list(sig.index) == list(ids)
+    r = pkg("pfml_input_data").rff(pn.feats[0], W=pn.W)
+    assert relerr(r["X_cos"], np.cos(pn.feats[0] @ pn.W)) < 1e-14 and relerr(r["X_sin"], np.sin(pn.feats[0] @ pn.W)) < 1e-14
+    assert GF.create_lambda({1: 0.1, 2: 0.2, 3: 0.3}, [3, 1]).tolist() == [[0.3, 0.0], [0.0, 0.1]]
