@@ -125,34 +125,78 @@ def make_panel(N=500, T=24, p=64, g=np.exp(-3.0), seed=1, F=N_FEATURES, ragged=0
                  ivol=ivol, barra_has=barra_has, W=W, meta=dict(seed=seed, g=float(g)))
 
 
-def make_daily(N=60, years=12, seed=3, start="2008-01-01", F=N_FEATURES):
-    """Daily panel for the Barra/EWMA covariance estimator ("Estimate Covariance Matrix.py"), SURVEY C2.
+def make_daily(N=60, years=3.2, seed=3, start="2015-01-01", F=N_FEATURES, miss=0.02):
+    """Daily panel for the Barra/EWMA covariance estimator ("Estimate Covariance Matrix.py"), SURVEY config C2.
 
-    Returns a dict of dense arrays: business days, per-(month, stock) characteristics + cluster map,
-    daily excess returns ret = X f + e with NaNs for missing observations."""
+    Returns a dict of dense arrays: business days [D], month-ends [Tm] (one lagged month in front), ids [N],
+    monthly characteristics feats [Tm,N,F] in [0,1], valid [Tm,N], direction [F] (+-1), cluster_of [F] (0..12),
+    ff12 [N] (1..12), size_grp [N], daily excess returns ret [D,N] = X f + e with NaN where unobserved."""
     rng = np.random.default_rng(seed)
-    days = np.arange(np.datetime64(start, "D"), np.datetime64(start, "D") + np.timedelta64(int(366 * years), "D"))
-    dow = (days.astype("datetime64[D]").view("int64") - 4) % 7      # 1970-01-01 is a Thursday
-    days = days[(dow != 5) & (dow != 6)]                            # Monday=0 .. Friday=4 kept
+    days = np.arange(np.datetime64(start, "D"), np.datetime64(start, "D") + np.timedelta64(int(365.25 * years), "D"))
+    dow = (days.view("int64") - 4) % 7                                # 1970-01-01 is a Thursday; Monday = 0
+    days = days[dow < 5]
     months = np.unique(days.astype("datetime64[M]"))
-    Tm = len(months) + 1                                            # one extra lagged month in front
-    month_ends = ((np.concatenate([[months[0] - 1], months]) + 1).astype("datetime64[D]") - np.timedelta64(1, "D"))
+    mlist = np.concatenate([[months[0] - 1], months])
+    month_ends = (mlist + 1).astype("datetime64[D]") - np.timedelta64(1, "D")
+    Tm, D = len(month_ends), len(days)
     ids = 10001 + np.arange(N, dtype=np.int64)
-    feats = rng.random((Tm, N, F))
+    feats = np.round(rng.random((Tm, N, F)) * 1000.0) / 1000.0      # 3-decimal ranks: golden files store them as uint16
+    valid = rng.random((Tm, N)) >= 0.03
     direction = rng.choice([-1, 1], F)
     cluster_of = np.arange(F) % N_CLUSTER
     rng.shuffle(cluster_of)
-    ff12 = rng.integers(1, N_IND + 1, N)
+    ff12 = (np.arange(N) % N_IND) + 1
+    rng.shuffle(ff12)
     size_grp = rng.choice(np.array(["mega", "large", "small"]), N)
     K = N_IND + N_CLUSTER
     A = rng.standard_normal((K, K))
-    C = A @ A.T / K
+    f = 0.005 * rng.standard_normal((D, K)) @ (A / np.sqrt(K)).T
     sig = rng.uniform(0.008, 0.03, N)
-    D = len(days)
-    f = (0.005 * np.linalg.cholesky(C) @ rng.standard_normal((K, D))).T      # [D, K]
-    e = sig[None, :] * rng.standard_normal((D, N))
-    return dict(days=days, month_ends=month_ends, ids=ids, feats=feats, direction=direction,
-                cluster_of=cluster_of, ff12=ff12, size_grp=size_grp, f_true=f, e=e, seed=seed)
+    load = np.concatenate([np.eye(N_IND)[ff12 - 1], rng.standard_normal((N, N_CLUSTER))], axis=1)
+    ret = f @ load.T + sig[None, :] * rng.standard_normal((D, N))
+    ret[rng.random((D, N)) < miss] = np.nan
+    late = rng.integers(0, N)                                          # one stock lists late: coverage filter + median fill
+    ret[: D // 2, late] = np.nan
+    return dict(days=days, month_ends=month_ends, ids=ids, feats=feats, valid=valid, direction=direction,
+                cluster_of=cluster_of, ff12=ff12, size_grp=size_grp, ret=ret, seed=seed)
+
+
+def write_covariance_artefacts(daily, path, features=None):
+    """Files "Estimate Covariance Matrix.py" reads: Factors_processed (JKP_US_SP500.db), d_ret_ex
+    (crsp_daily_SP500.db), cluster_labels_processed.csv (:40-106)."""
+    import os
+    import sqlite3
+
+    import pandas as pd
+    if features is None:
+        from .general_functions import get_features
+        features = get_features(True)
+    data = os.path.join(path, "Data")
+    os.makedirs(data, exist_ok=True)
+    Tm, N, F = daily["feats"].shape
+    me = pd.to_datetime(daily["month_ends"])
+    rows = {
+        "id": np.tile(daily["ids"], Tm), "eom": np.repeat(me.strftime("%Y-%m-%d 00:00:00").values, N),
+        "sic": 0, "ff49": 0, "size_grp": np.tile(daily["size_grp"], Tm), "me": 1.0, "crsp_exchcd": 1, "dolvol": 1.0,
+        "lambda": 1e-8, "rvol_m": 0.0, "tr_ld0": 0.0,
+        "eom_ret": np.repeat((me + pd.offsets.MonthEnd(1)).strftime("%Y-%m-%d 00:00:00").values, N),
+        "ret_ld1": 0.0, "tr_ld1": 0.0, "mu_ld0": 0.0, "ff12": np.tile(daily["ff12"].astype(str), Tm),
+        "valid": daily["valid"].reshape(-1).astype(int),
+    }
+    df = pd.concat([pd.DataFrame(rows), pd.DataFrame(daily["feats"].reshape(Tm * N, F), columns=features)], axis=1)
+    con = sqlite3.connect(os.path.join(data, "JKP_US_SP500.db"))
+    df.to_sql("Factors_processed", con, if_exists="replace", index=False)
+    con.close()
+    D = len(daily["days"])
+    dd = pd.DataFrame({"permno": np.tile(daily["ids"], D),
+                       "date": np.repeat(pd.to_datetime(daily["days"]).strftime("%Y-%m-%d 00:00:00").values, N),
+                       "ret_excess": daily["ret"].reshape(-1)})
+    con = sqlite3.connect(os.path.join(data, "crsp_daily_SP500.db"))
+    dd.to_sql("d_ret_ex", con, if_exists="replace", index=False)
+    con.close()
+    pd.DataFrame({"characteristic": features, "direction": daily["direction"],
+                  "cluster": [f"cl{c:02d}" for c in daily["cluster_of"]]}).to_csv(
+        os.path.join(data, "cluster_labels_processed.csv"), index=False)
 
 
 def write_reference_artefacts(panel, path, features=None):

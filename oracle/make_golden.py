@@ -138,6 +138,26 @@ def main():
                         m_mu=pn.mu, m_ref=m_ref, wc_X=X, wc_w=wts, cov_ref=cov_ref, cor_ref=cor_ref,
                         ev_x=xs, ev_lam=lam_e, ev_ref=ev_ref,
                         feat_idx_4=feat_idx[4], feat_idx_8=feat_idx[8], feat_idx_16=feat_idx[16])
+    # ---------------- script-level golden: "Estimate Covariance Matrix.py" -----------------
+    daily = syn.make_daily()
+    cov_set = dict(obs=400, hl_cor=150, hl_var=60, hl_stock_var=60, initial_var_obs=40)
+    with tempfile.TemporaryDirectory() as tmp:
+        barra = H.run_cov_script(daily, tmp + "/", cov_set)
+    keys = sorted(barra.keys())
+    N = len(daily["ids"])
+    K = barra[keys[0]]["fct_cov"].shape[0]
+    load = np.full((len(keys), N, K), np.nan); ivol = np.full((len(keys), N), np.nan)
+    fcov = np.stack([barra[k]["fct_cov"].to_numpy() for k in keys])
+    for c, k in enumerate(keys):
+        ii = np.searchsorted(daily["ids"], np.asarray(barra[k]["fct_load"].index))
+        load[c, ii] = barra[k]["fct_load"].to_numpy()
+        ivol[c, ii] = barra[k]["ivol_vec"].to_numpy()
+    np.savez_compressed(os.path.join(gold, "cov_ref_small.npz"), calc_dates=np.array([np.datetime64(k.date()) for k in keys]),
+                        fct_load=load, fct_cov=fcov, ivol=ivol, factor_cols=np.array(list(barra[keys[0]]["fct_cov"].columns)),
+                        cov_set=np.array([cov_set[k] for k in ("obs", "hl_cor", "hl_var", "hl_stock_var", "initial_var_obs")]),
+                        daily_feats_q=np.round(daily["feats"] * 1000.0).astype(np.uint16),
+                        **{"daily_" + k: v for k, v in daily.items() if k not in ("seed", "feats")})
+    print("covariance script golden:", len(keys), "calc dates", keys[0].date(), "..", keys[-1].date())
     print("golden fixtures written to", gold)
 
 

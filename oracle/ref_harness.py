@@ -94,3 +94,23 @@ def run_search_coef(panel, path, p_vec, l_vec, start_year, end_yr):
     run_script("PFML_Search_Coef.py", path)
     with open(os.path.join(path, "Data", "coef_dict_0.pkl"), "rb") as f:
         return pickle.load(f)[0]
+
+
+def run_cov_script(daily, path, cov_set):
+    """exec "Estimate Covariance Matrix.py" on a synthetic daily panel; returns the Barra_Cov dict it pickles."""
+    import importlib
+    GF = _import_general_functions()
+    syn = importlib.import_module("jkmp22-machine-learning-and-the-implementable-efficient-frontier-replication_b200.synthetic")
+    syn.write_covariance_artefacts(daily, path, GF.get_features(True))
+    orig = GF._orig_get_settings if hasattr(GF, "_orig_get_settings") else GF.get_settings
+    GF._orig_get_settings = orig
+
+    def get_settings():
+        settings, pf_set = orig()
+        settings["cov_set"].update(cov_set)
+        return settings, pf_set
+
+    GF.get_settings = get_settings
+    run_script("Estimate Covariance Matrix.py", path)
+    with open(os.path.join(path, "Data", "Barra_Cov.pkl"), "rb") as f:
+        return pickle.load(f)
