@@ -342,7 +342,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dates", type=int, default=148, help="date-steps per step per GPU")
-    ap.add_argument("--chunk", type=int, default=37, help="dates per device chunk in the host entry point")
+    ap.add_argument("--chunk", type=int, default=0, help="dates per device chunk in the host entry point (0 = library schedule)")
     ap.add_argument("--profile-only", action="store_true", help="resident-path steps only (for ncu launch lists)")
     ap.add_argument("--gemm-only", action="store_true", help="the dominant GEMM shape alone (for ncu --set full)")
     args = ap.parse_args()

@@ -5,7 +5,9 @@
 // chunks.  Chunk c computes on the compute stream into staging buffer c%2 while the copy stream drains
 // chunk c-1 to the caller's host buffers, so PCIe D2H (29 MB per date at p = 1024) overlaps the DMMA work.
 // Device memory comes from a grow-only per-device arena that is reused across calls.
+#include <cstdlib>
 #include <mutex>
+#include <vector>
 
 #include "kernels.cuh"
 #include "pfml_b200.h"
@@ -17,7 +19,8 @@ namespace {
 struct Arena {
   void* base = nullptr;
   size_t cap = 0;
-  cudaStream_t compute = nullptr, copy = nullptr;
+  cudaStream_t compute = nullptr, compute2 = nullptr, copy = nullptr;
+  cudaEvent_t panel_ready = nullptr;
   cudaEvent_t computed[2] = {nullptr, nullptr}, drained[2] = {nullptr, nullptr};
   bool init = false;
 };
@@ -40,7 +43,7 @@ struct HostPlan {
   unsigned char* has;
   int *date_t, *sel, *n_sel, *status;
   double* stage[2];
-  void* ws;
+  void* ws[2];
   size_t ws_bytes, stage_doubles, total;
 };
 
@@ -60,11 +63,14 @@ HostPlan plan(void* base, const pfml_host_block_t* b, int B, int NP, int chunk, 
   h.vol_scale = m.take<double>(TN); h.gt = m.take<double>(TN);
   h.has = m.take<unsigned char>(TN);
   h.date_t = m.take<int>(B); h.sel = m.take<int>((size_t)B * NP); h.n_sel = m.take<int>(B); h.status = m.take<int>(B);
-  h.stage_doubles = (size_t)chunk * (P + P * P * (1 + (want_risk ? 1 : 0) + (want_tc ? 1 : 0)) + (want_sig ? (size_t)NP * P : 0));
+  // device copy of ALL outputs of the call (B dates): no staging buffer has to be recycled, so a chunk never waits
+  // for an earlier chunk's download
+  h.stage_doubles = (size_t)B * (P + P * P * (1 + (want_risk ? 1 : 0) + (want_tc ? 1 : 0)) + (want_sig ? (size_t)NP * P : 0));
   h.stage[0] = m.take<double>(h.stage_doubles);
-  h.stage[1] = m.take<double>(h.stage_doubles);
+  h.stage[1] = nullptr;
   h.ws_bytes = ws_bytes;
-  h.ws = m.take<char>(ws_bytes);
+  h.ws[0] = m.take<char>(ws_bytes);
+  h.ws[1] = m.take<char>(ws_bytes);
   h.total = m.off;
   return h;
 }
@@ -82,13 +88,35 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
     set_error("pfml_date_steps_host: bad device %d", device);
     return -1;
   }
-  if (chunk <= 0 || chunk > B) chunk = B;
+  // Chunks: uniform, default ceil(B / 6).  Consecutive chunks alternate between two compute streams (each with its
+  // own workspace and staging buffer): the latency-bound kernels of one chunk (block inverses, small GEMMs of the
+  // recursion) overlap the DMMA-bound kernels of the other, and the copy stream drains finished chunks meanwhile.
+  std::vector<int> sched;
+  if (const char* e = getenv("PFML_HOST_SCHED")) {        // tuning aid: explicit comma-separated chunk sizes
+    int left = B;
+    for (const char* q = e; *q && left > 0;) {
+      int v = atoi(q);
+      if (v <= 0) break;
+      v = v < left ? v : left;
+      sched.push_back(v); left -= v;
+      while (*q && *q != ',') q++;
+      if (*q == ',') q++;
+    }
+    if (left > 0) sched.push_back(left);
+  } else {
+    if (chunk <= 0) chunk = B <= 40 ? B : (B + 5) / 6;      // measured best on B200 (tools/e2e_chunk_sweep.py)
+    for (int b0 = 0; b0 < B; b0 += chunk) sched.push_back((B - b0) < chunk ? (B - b0) : chunk);
+  }
+  chunk = 0;
+  for (int c : sched) chunk = c > chunk ? c : chunk;      // buffers are sized for the largest chunk
   std::lock_guard<std::mutex> lk(g_arena_mu);
   PFML_CUDA_OK(cudaSetDevice(device));
   Arena& a = g_arena[device];
   if (!a.init) {
     PFML_CUDA_OK(cudaStreamCreateWithFlags(&a.compute, cudaStreamNonBlocking));
+    PFML_CUDA_OK(cudaStreamCreateWithFlags(&a.compute2, cudaStreamNonBlocking));
     PFML_CUDA_OK(cudaStreamCreateWithFlags(&a.copy, cudaStreamNonBlocking));
+    PFML_CUDA_OK(cudaEventCreateWithFlags(&a.panel_ready, cudaEventDisableTiming));
     for (int i = 0; i < 2; i++) {
       PFML_CUDA_OK(cudaEventCreateWithFlags(&a.computed[i], cudaEventDisableTiming));
       PFML_CUDA_OK(cudaEventCreateWithFlags(&a.drained[i], cudaEventDisableTiming));
@@ -110,6 +138,7 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
   }
   h = plan(a.base, blk, B, NP, chunk, risk != nullptr, tc != nullptr, signal_t != nullptr, ws_bytes);
   cudaStream_t cs = a.compute, ds = a.copy;
+  cudaStream_t cstream[2] = {a.compute, a.compute2};
 
   // ---- upload the block ---------------------------------------------------------------------------
 #define H2D(dst, src, count, type) PFML_CUDA_OK(cudaMemcpyAsync(dst, src, (size_t)(count) * sizeof(type), cudaMemcpyHostToDevice, cs))
@@ -137,20 +166,28 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
   pan.rff = h.rff; pan.vol_scale = h.vol_scale; pan.gt = h.gt; pan.lam = h.lam; pan.ret_ld1 = h.ret;
   pan.fct_load = h.fct_load; pan.fct_cov = h.fct_cov; pan.ivol = h.ivol; pan.wealth = h.wealth; pan.rf = h.rf;
 
-  // ---- chunks: compute on `cs`, drain on `ds` ----------------------------------------------------
-  int n_chunks = (B + chunk - 1) / chunk;
-  for (int c = 0; c < n_chunks; c++) {
-    const int b0 = c * chunk, nb = (B - b0) < chunk ? (B - b0) : chunk, sb = c & 1;
-    double* st = h.stage[sb];
-    double* d_rt = st;              st += (size_t)chunk * P;
-    double* d_den = st;             st += (size_t)chunk * P * P;
-    double* d_risk = nullptr; if (risk) { d_risk = st; st += (size_t)chunk * P * P; }
-    double* d_tc = nullptr;   if (tc) { d_tc = st; st += (size_t)chunk * P * P; }
-    double* d_sig = nullptr;  if (signal_t) { d_sig = st; st += (size_t)chunk * NP * P; }
-    if (c >= 2) PFML_CUDA_OK(cudaStreamWaitEvent(cs, a.drained[sb], 0));
+  PFML_CUDA_OK(cudaEventRecord(a.panel_ready, cs));
+  PFML_CUDA_OK(cudaStreamWaitEvent(a.compute2, a.panel_ready, 0));
+  // ---- chunks: compute on two alternating streams, drain on `ds` -----------------------------------
+  const int n_chunks = (int)sched.size();
+  const bool trace = getenv("PFML_HOST_TRACE") != nullptr;
+  std::vector<cudaEvent_t> tev;
+  auto mark = [&](cudaStream_t st) { if (trace) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); tev.push_back(e); } };
+  mark(cs);
+  int b0 = 0;
+  for (int c = 0; c < n_chunks; b0 += sched[c], c++) {
+    const int nb = sched[c], sb = c & 1;
+    double* st = h.stage[0];
+    double* d_rt = st + (size_t)b0 * P;                     st += (size_t)B * P;
+    double* d_den = st + (size_t)b0 * P * P;                st += (size_t)B * P * P;
+    double* d_risk = nullptr; if (risk) { d_risk = st + (size_t)b0 * P * P; st += (size_t)B * P * P; }
+    double* d_tc = nullptr;   if (tc) { d_tc = st + (size_t)b0 * P * P; st += (size_t)B * P * P; }
+    double* d_sig = nullptr;  if (signal_t) { d_sig = st + (size_t)b0 * NP * P; st += (size_t)B * NP * P; }
+    cudaStream_t ks = cstream[sb];
     PFML_TRY(pfml_date_steps(&pan, nb, n_max, h.date_t + b0, h.sel + (size_t)b0 * NP, h.n_sel + b0, d_rt, d_den, d_risk, d_tc,
-                             d_sig, h.status + b0, h.ws, h.ws_bytes, cs));
-    PFML_CUDA_OK(cudaEventRecord(a.computed[sb], cs));
+                             d_sig, h.status + b0, h.ws[sb], h.ws_bytes, ks));
+    PFML_CUDA_OK(cudaEventRecord(a.computed[sb], ks));
+    mark(ks);
     PFML_CUDA_OK(cudaStreamWaitEvent(ds, a.computed[sb], 0));
 #define D2H(dst, src, count) PFML_CUDA_OK(cudaMemcpyAsync(dst, src, (size_t)(count) * sizeof(double), cudaMemcpyDeviceToHost, ds))
     D2H(r_tilde + (size_t)b0 * P, d_rt, (size_t)nb * P);
@@ -160,9 +197,21 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
     if (signal_t) D2H(signal_t + (size_t)b0 * NP * P, d_sig, (size_t)nb * NP * P);
 #undef D2H
     PFML_CUDA_OK(cudaEventRecord(a.drained[sb], ds));
+    mark(ds);
   }
-  if (status) PFML_CUDA_OK(cudaMemcpyAsync(status, h.status, sizeof(int) * B, cudaMemcpyDeviceToHost, cs));
-  PFML_CUDA_OK(cudaStreamSynchronize(cs));
+  PFML_CUDA_OK(cudaStreamSynchronize(a.compute));
+  PFML_CUDA_OK(cudaStreamSynchronize(a.compute2));
+  if (status) PFML_CUDA_OK(cudaMemcpyAsync(status, h.status, sizeof(int) * B, cudaMemcpyDeviceToHost, ds));
   PFML_CUDA_OK(cudaStreamSynchronize(ds));
+  if (trace) {
+    fprintf(stderr, "[pfml host trace] panel ready at 0 ms;");
+    for (size_t i = 1; i < tev.size(); i++) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, tev[0], tev[i]);
+      fprintf(stderr, " %s%zu %.1f", (i & 1) ? "computed" : "drained", (i - 1) / 2, ms);
+    }
+    fprintf(stderr, "\n");
+    for (auto e : tev) cudaEventDestroy(e);
+  }
   return 0;
 }
