@@ -164,6 +164,36 @@ def run_reference(args, rank, world):
                 "faster than the reference script itself"}))
 
 
+def hp_grid_walltime(torch, dev, runner, B):
+    """hp-grid wall-time (BASELINE metric, second half): PFML_Search_Coef.py over the step's own r_tilde / denom,
+    treated as B consecutive months: expanding-window sums + ridge solves for 15 lambda x p in {64..1024} x all
+    complete years, on the device; the same grid for ONE year on the host (numpy LU, all cores) for comparison."""
+    sc = importlib.import_module(PKG + ".pfml_search_coef")
+    syn = importlib.import_module(PKG + ".synthetic")
+    import pfml_oracle as O
+    month_ends = syn.month_end_range("1990-01", B)
+    years = list(range(1993, 1990 + B // 12 + 1))
+    p_vec = [64, 128, 256, 512, 1024]
+    l_vec = [0.0] + list(np.exp(np.linspace(-10, 10, 14)))
+    rt, dn = runner.r_tilde, runner.denom
+    sc.search_coef(rt, dn, month_ends, years, p_vec, l_vec, device=dev)          # warm-up
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    coef = sc.search_coef(rt, dn, month_ends, years, p_vec, l_vec, device=dev)
+    torch.cuda.synchronize(dev)
+    gpu_s = time.perf_counter() - t0
+    use_all_host_threads()
+    t0 = time.perf_counter()
+    ref = O.search_coef(rt.cpu().numpy(), dn.cpu().numpy(), month_ends, years[:1], p_vec, l_vec)
+    cpu_s_per_year = time.perf_counter() - t0
+    y, p = years[0], 1024
+    err = max(float(np.max(np.abs(coef[y][p][j] - ref[y][p][j])) / np.max(np.abs(ref[y][p][j]))) for j in range(1, len(l_vec)))
+    return {"years": len(years), "n_lambda": len(l_vec), "p_vec": p_vec, "solves": len(years) * len(l_vec) * len(p_vec),
+            "gpu_wall_s": gpu_s, "cpu_port_wall_s_per_year": cpu_s_per_year, "cpu_port_wall_s_extrapolated": cpu_s_per_year * len(years),
+            "speedup_vs_cpu_port": cpu_s_per_year * len(years) / gpu_s, "max_rel_err_vs_cpu_p1024_lambda_gt_0": err,
+            "includes": "bucket sums, cumulative sums, gather of the pfml_feat_fun(p) sub-matrices, inverses, refinement, D2H of beta"}
+
+
 def measure_fp64_peak(torch, dev):
     n = 8192
     a = torch.randn(n, n, dtype=torch.float64, device=dev)
@@ -286,18 +316,24 @@ def run_ours(args, rank, world, local_rank):
 
     if rank != 0:
         return
-    # ---- roofline of the dominant kernel -------------------------------------------------------------
+    # ---- roofline of the dominant kernel ---------------------------------------------------------------
+    # The dominant launch is the Horner step m~ [n x n] @ Z [n x P] for the whole batch (12 launches per step, all
+    # the same shape; SURVEY 8d counts them as 24 n^2 P flops per date = 2 n^2 P per launch and date).  Its duration
+    # is the `horner_nxP` stage (CUDA events around those 12 launches plus one row-scaling kernel, < 1%) / 12.
     peak = measure_fp64_peak(torch, dev)
     off = official_flops_per_date()
+    horner_ms = pms[4] / args.steps
+    launch_ms = horner_ms / 12.0
+    flops_per_launch = 2.0 * N_STOCKS * N_STOCKS * (P_FEAT + 1) * B
+    achieved = flops_per_launch / (launch_ms * 1e-3) * 1e-12
     gemm_ms = pms[0] / args.steps                      # all DMMA GEMM launches of one step
     total_stage_ms = sum(pms[1:7]) / args.steps
-    achieved = off["total"] * B / (gemm_ms * 1e-3) * 1e-12
-    executed = pfl[0] / args.steps / (gemm_ms * 1e-3) * 1e-12
     traffic = None
     ncu_json = os.path.join(ROOT, "profiles", "ncu_summary.json")
     if os.path.exists(ncu_json):
         try:
-            traffic = json.load(open(ncu_json)).get("dmma_gemm_dram_bytes_per_launch")
+            per_date = json.load(open(ncu_json)).get("horner_gemm_dram_bytes_per_launch_per_date")
+            traffic = per_date * B if per_date else None
         except Exception:
             traffic = None
     stage_map = {"m_func": off["m_func"], "chain_nxn": 22 * N_STOCKS ** 3, "horner_nxP": 24 * N_STOCKS ** 2 * (P_FEAT + 1),
@@ -308,6 +344,7 @@ def run_ours(args, rank, world, local_rank):
         stages[names[i]] = {"ms_per_step": round(st_ms, 3), "share": round(st_ms / total_stage_ms, 4)}
         if names[i] in stage_map:
             stages[names[i]]["algorithmic_tflops"] = round(stage_map[names[i]] * B / (st_ms * 1e-3) * 1e-12, 2)
+    hp = hp_grid_walltime(torch, dev, runner, B)
     cpu_v, cpu_n, cpu_dt = cpu_dates_per_sec(syn)
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -321,13 +358,18 @@ def run_ours(args, rank, world, local_rank):
                 "outputs": "r_tilde, denom, risk, tc, signal_t (everything PFML_Input_Data.py stores per date)",
                 "chunk": args.chunk, "max_abs_diff_vs_resident_path": chk},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "pfml::gemm_kernel (batched FP64 DMMA GEMM, all launches of a step)",
+        "roofline": {"bound": "tensor", "kernel": "pfml::gemm_kernel<64,64,32,32,16,3,3> on the Horner step (batch x [512 x 1025 x 512], FP64 DMMA)",
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, best of 5, measured in this run "
                                     "(MEASURED_PEAKS.json has no FP64 figure; DMMA issue peak 37.05 TFLOP/s, profiles/r01_fp64_peak_microbench.log)",
-                     "algorithmic_flops_per_date": off["total"], "executed_tflops": executed,
-                     "gemm_ms_per_step": gemm_ms, "gemm_launches_per_step": pln[0] / args.steps,
-                     "gemm_share_of_step": gemm_ms / (ms_total / args.steps)},
+                     "algorithmic_flops_per_launch": flops_per_launch, "launch_ms": launch_ms, "launches_per_step": 12,
+                     "share_of_step": horner_ms / (ms_total / args.steps),
+                     "all_gemm_launches": {"algorithmic_tflops": off["total"] * B / (gemm_ms * 1e-3) * 1e-12,
+                                           "executed_tflops": pfl[0] / args.steps / (gemm_ms * 1e-3) * 1e-12,
+                                           "ms_per_step": gemm_ms, "launches_per_step": pln[0] / args.steps,
+                                           "share_of_step": gemm_ms / (ms_total / args.steps),
+                                           "algorithmic_flops_per_date": off["total"]}},
+        "hp_grid": hp,
         "stages": stages,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                          "sample": f"{cpu_n} date-steps of the same N=500, p=1024 workload in {cpu_dt:.1f} s (numpy oracle, all host BLAS threads)"},

@@ -109,6 +109,13 @@ def test_date_steps_n500_p128(dev, syn):
     _check_dates(dev.date_steps(panel, [12]), panel, [12], rff_x, vs)
 
 
+def test_date_steps_n700_uneven_recursion(dev, syn):
+    """n = 700 -> NP = 704 = 11 blocks of 64: uneven splits of the recursive block inverse (352 + 352 -> 192 + 160 ...)."""
+    panel = syn.make_panel(N=700, T=14, p=16, seed=28, ragged=0.01)
+    rff_x, vs = _panel_pre(panel)
+    _check_dates(dev.date_steps(panel, [12, 13]), panel, [12, 13], rff_x, vs)
+
+
 def test_nan_growth_semantics_q8(dev, syn):
     """NaN tr_ld0 in look-back months -> g = 1 (PFML_Input_Data.py:405); at date d it propagates to tc (:458)."""
     panel = syn.make_panel(N=80, T=15, p=16, seed=24, nan_tr=0.03)
