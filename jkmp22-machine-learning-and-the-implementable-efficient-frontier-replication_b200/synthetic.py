@@ -48,6 +48,18 @@ class Panel:
     lb: int = LB
     iterations: int = 10
     meta: dict = field(default_factory=dict)
+    me: np.ndarray = None      # [T, N] market equity (initial value weights of the back-test, PFML_best_hps.py:143-147)
+    tr_ld1: np.ndarray = None  # [T, N] lead total return (weight drift, PFML_best_hps.py:199)
+    mu_ld1: np.ndarray = None  # [T]    lead market return (wealth_processed.csv 'mu_ld1')
+
+    def __post_init__(self):
+        T, N = self.valid.shape
+        if self.me is None:
+            self.me = np.ones((T, N))
+        if self.tr_ld1 is None:
+            self.tr_ld1 = np.zeros((T, N))
+        if self.mu_ld1 is None:
+            self.mu_ld1 = np.zeros(T)
 
     @property
     def T(self):
@@ -72,7 +84,7 @@ def month_end_range(start="2010-01", periods=24):
 
 
 def make_panel(N=500, T=24, p=64, g=np.exp(-3.0), seed=1, F=N_FEATURES, ragged=0.0,
-               barra_missing=0.0, start="2010-01", nan_tr=0.0) -> Panel:
+               barra_missing=0.0, start="2010-01", nan_tr=0.0, quantize=False) -> Panel:
     """Draw a panel.  ``ragged``: probability that a stock is invalid in a month (the universe then
     differs by date); ``barra_missing``: probability that an id is absent from the Barra object of a
     month (exercises the eom-median fill of vol_scale, PFML_Input_Data.py:300-305; only applied to
@@ -82,6 +94,8 @@ def make_panel(N=500, T=24, p=64, g=np.exp(-3.0), seed=1, F=N_FEATURES, ragged=0
     K = N_IND + N_CLUSTER
     ids = 10001 + np.arange(N, dtype=np.int64)
     feats = rng.random((T, N, F))
+    if quantize:                     # 3-decimal ranks: golden files can store them as uint16
+        feats = np.round(feats * 1000.0) / 1000.0
     valid = np.ones((T, N), dtype=bool)
     if ragged > 0:
         # a stock drops out for a stretch; validity needs all 13 look-back rows, which the dense panel has
@@ -120,7 +134,11 @@ def make_panel(N=500, T=24, p=64, g=np.exp(-3.0), seed=1, F=N_FEATURES, ragged=0
         barra_has |= valid          # create_cov(cov_list[d], ids) needs every universe id
         # look-back rows of later universes may still be missing -> median fill path
     W = np.sqrt(g) * rng.standard_normal((F, p // 2))
-    return Panel(ids=ids, month_ends=month_end_range(start, T), feats=feats, valid=valid, ret_ld1=ret_ld1,
+    rng2 = np.random.default_rng(seed + 100003)          # extra fields drawn from a separate stream
+    me = np.exp(np.log(1e9) + 1.5 * rng2.standard_normal(N))[None, :] * np.exp(0.05 * rng2.standard_normal((T, N)))
+    tr_ld1 = np.clip(0.008 + 0.08 * rng2.standard_normal((T, N)), -0.9, None)
+    mu_ld1 = 0.008 + 0.04 * rng2.standard_normal(T)
+    return Panel(me=me, tr_ld1=tr_ld1, mu_ld1=mu_ld1, ids=ids, month_ends=month_end_range(start, T), feats=feats, valid=valid, ret_ld1=ret_ld1,
                  tr_ld0=tr, mu_ld0=mu_ld0, lam=lam, wealth=wealth, rf=rf, fct_load=fct_load, fct_cov=fct_cov,
                  ivol=ivol, barra_has=barra_has, W=W, meta=dict(seed=seed, g=float(g)))
 
@@ -218,10 +236,10 @@ def write_reference_artefacts(panel, path, features=None):
     rows = {
         "id": np.tile(panel.ids, T),
         "eom": np.repeat(me.strftime("%Y-%m-%d 00:00:00").values, N),
-        "sic": 0, "ff49": 0, "size_grp": "large", "me": 1.0, "crsp_exchcd": 1, "dolvol": 1.0,
+        "sic": 0, "ff49": 0, "size_grp": "large", "me": panel.me.reshape(-1), "crsp_exchcd": 1, "dolvol": 1.0,
         "lambda": panel.lam.reshape(-1), "rvol_m": 0.0, "tr_ld0": panel.tr_ld0.reshape(-1),
         "eom_ret": np.repeat((me + pd.offsets.MonthEnd(1)).strftime("%Y-%m-%d 00:00:00").values, N),
-        "ret_ld1": panel.ret_ld1.reshape(-1), "tr_ld1": 0.0, "mu_ld0": panel.mu_ld0.reshape(-1),
+        "ret_ld1": panel.ret_ld1.reshape(-1), "tr_ld1": panel.tr_ld1.reshape(-1), "mu_ld0": panel.mu_ld0.reshape(-1),
         "ff12": "1", "valid": panel.valid.reshape(-1).astype(int),
     }
     df = pd.concat([pd.DataFrame(rows), pd.DataFrame(panel.feats.reshape(T * N, F), columns=features)], axis=1)
@@ -230,7 +248,7 @@ def write_reference_artefacts(panel, path, features=None):
     con.close()
     pd.DataFrame({"yyyymm": me.strftime("%Y%m").astype(int), "RF": panel.rf * 100.0}).to_csv(
         os.path.join(data, "FF_RF_monthly.csv"), index=False)
-    pd.DataFrame({"eom": me, "wealth": panel.wealth, "mu_ld1": 0.0}).to_csv(
+    pd.DataFrame({"eom": me, "wealth": panel.wealth, "mu_ld1": panel.mu_ld1}).to_csv(
         os.path.join(data, "wealth_processed.csv"), index=False)
     names = [f"f{k}" for k in range(panel.fct_cov.shape[1])]
     barra = {}

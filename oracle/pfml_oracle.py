@@ -281,3 +281,89 @@ def daily_ols(X, y):
     except np.linalg.LinAlgError:
         coef = np.linalg.pinv(XtX) @ Xty
     return coef, y - X @ coef
+
+
+# ----------------------------------------------------------------------------------------------
+# f1: validation utility (PFML_hp_reals.py), f2: aim portfolio (PFML_aim_fun.py), f3: back-test (PFML_best_hps.py)
+# ----------------------------------------------------------------------------------------------
+def hp_reals(r_tilde, denom, month_ends, coef, hp_years, p_vec, l_vec):
+    """PFML_hp_reals.py:73-122 for one g.  Returns a dict of equal-length arrays sorted by (p, l, eom_ret):
+    eom, eom_ret (datetime64[D]), obj, l, p, hp_end, cum_obj, rank."""
+    import pandas as pd
+    d_all = np.asarray(month_ends).astype("datetime64[D]")
+    p_max = r_tilde.shape[1] - 1
+    rows = []
+    for end in sorted(int(y) for y in hp_years):                                    # :73
+        idx = np.flatnonzero((d_all >= np.datetime64(f"{end - 1}-12-31")) & (d_all <= np.datetime64(f"{end}-11-30")))   # :76
+        for p in p_vec:                                                             # :81
+            fi = pfml_feat_idx(p, p_max)
+            for i in range(len(l_vec)):                                             # :88
+                b = coef[end][p][i]
+                for t in idx:                                                       # :91
+                    rt, dn = r_tilde[t][fi], denom[t][np.ix_(fi, fi)]
+                    r = rt.T @ b - 0.5 * b.T @ dn @ b                               # :95
+                    rows.append((d_all[t], r, i, p, end))
+    df = pd.DataFrame(rows, columns=["eom", "obj", "l", "p", "hp_end"])
+    df["eom"] = pd.to_datetime(df["eom"])
+    df["eom_ret"] = df["eom"] + pd.offsets.MonthEnd(1)                              # :97
+    df = df.sort_values(["p", "l", "eom_ret"])                                      # :106
+    df["cum_obj"] = df.groupby(["p", "l"])["obj"].expanding().mean().reset_index(level=[0, 1], drop=True)   # :109-115
+    df["rank"] = df.groupby("eom_ret")["cum_obj"].rank(ascending=False, method="dense")                  # :118-122
+    return df.reset_index(drop=True)
+
+
+def aim_portfolios(validation, coef, signal_t, month_ends, dates_oos_idx, ids_by_date):
+    """PFML_aim_fun.py:126-163 for one g: per OOS date the rank-1 (p, l) of the previous December and
+    w_aim = signal_t[d][feat] @ beta.  ``signal_t[t]`` [n_t, P] in feat_all order; returns {t: (p, l, w_aim)}."""
+    import pandas as pd
+    v = validation
+    opt = v[(v["eom_ret"].dt.month == 12) & (v["rank"] == 1)].assign(hp_end=lambda x: x["eom_ret"].dt.year)[["hp_end", "l", "p"]].reset_index(drop=True)
+    out = {}
+    for t in dates_oos_idx:
+        d = pd.Timestamp(month_ends[t])
+        oos_year = (d + pd.offsets.MonthEnd(1)).year                                # :136-138
+        h = opt[opt["hp_end"] == oos_year - 1]
+        p, l = int(h["p"].values[0]), int(h["l"].values[0])                         # first rank-1 row, :144-149
+        P = signal_t[t].shape[1]
+        fi = pfml_feat_idx(p, P - 1)
+        b = coef[oos_year][p][l]
+        out[t] = (p, l, signal_t[t][:, fi] @ b)                                     # :152
+    return out
+
+
+def pfml_w(panel, dates_idx, w_aim, vol_scale=None):
+    """pfml_w of PFML_best_hps.py:168-216 on the dense panel: value-weighted start at the first date, then
+    w = m w_start + (I - m) w_aim (:195), drift w_start' = w (1 + tr_ld1) / (1 + mu_ld1) (:199), new stocks start at 0.
+    ``w_aim[t]`` is aligned with the valid ids of date t.  Returns {t: dict(ids, w_start, w)}."""
+    out = {}
+    prev = None
+    for k, t in enumerate(dates_idx):
+        sel = np.flatnonzero(panel.valid[t])
+        n = len(sel)
+        if k == 0:
+            w_start = panel.me[t, sel] / panel.me[t, sel].sum()                     # :143-147
+        else:
+            w_start = np.zeros(n)                                                   # :210
+            pos = {int(i): j for j, i in enumerate(prev[0])}
+            for j, i in enumerate(sel):
+                if int(i) in pos:
+                    w_start[j] = prev[1][pos[int(i)]]
+        sigma = create_cov(panel.fct_load[t][sel], panel.fct_cov[t], panel.ivol[t, sel])
+        m = m_func(panel.wealth[t], panel.mu, panel.rf[t], sigma * panel.gamma_rel, panel.gamma_rel,
+                   create_lambda(panel.lam[t, sel]), panel.iterations)               # :186-190
+        w = m @ w_start + (np.eye(n) - m) @ w_aim[t]                                # :195
+        nxt = w * (1 + panel.tr_ld1[t, sel]) / (1 + panel.mu_ld1[t])                # :199 (mu_ld1 of wealth at eom d)
+        out[t] = dict(ids=panel.ids[sel], w_start=w_start, w=w)
+        prev = (sel, nxt)
+    return out
+
+
+def pf_stats(panel, weights):
+    """compute_stats / pf_ts_fun of PFML_best_hps.py:220-259 per date: inv, shorting, turnover, r, tc."""
+    out = {}
+    for t, o in weights.items():
+        sel = np.flatnonzero(panel.valid[t])
+        w, ws = o["w"], o["w_start"]
+        out[t] = dict(inv=np.sum(np.abs(w)), shorting=np.sum(np.abs(w[w < 0])), turnover=np.sum(np.abs(w - ws)),
+                      r=np.sum(w * panel.ret_ld1[t, sel]), tc=(panel.wealth[t] / 2) * np.sum(panel.lam[t, sel] * (w - ws) ** 2))
+    return out

@@ -114,3 +114,48 @@ def run_cov_script(daily, path, cov_set):
     run_script("Estimate Covariance Matrix.py", path)
     with open(os.path.join(path, "Data", "Barra_Cov.pkl"), "rb") as f:
         return pickle.load(f)
+
+
+def run_hp_reals(panel, path, p_vec, l_vec, start_year, end_yr):
+    """exec PFML_hp_reals.py (needs pfml_input_0.pkl and coef_dict_0.pkl under path); returns validation.csv."""
+    GF = _import_general_functions()
+    _settings_wrapper(GF, panel, p_vec, l_vec, start_year, end_yr)
+    run_script("PFML_hp_reals.py", path)
+    return pd.read_csv(os.path.join(path, "Data", "validation.csv"), parse_dates=["eom", "eom_ret"])
+
+
+def run_aim_fun(panel, path, p_vec, l_vec, start_year, end_yr, split_years):
+    """exec PFML_aim_fun.py; the script hard-codes test_end = 2023-12-31 at :94, which is patched to the panel's."""
+    GF = _import_general_functions()
+    _settings_wrapper(GF, panel, p_vec, l_vec, start_year, end_yr)
+    inner = GF.get_settings
+
+    def get_settings():
+        settings, pf_set = inner()
+        settings["pf"]["dates"]["split_years"] = split_years
+        return settings, pf_set
+
+    GF.get_settings = get_settings
+    te = pd.Timestamp(panel.month_ends[-1]).strftime("%Y-%m-%d")
+    run_script("PFML_aim_fun.py", path, patches=[("settings['split']['test_end'] = pd.to_datetime('2023-12-31')",
+                                                  f"settings['split']['test_end'] = pd.to_datetime('{te}')")])
+    with open(os.path.join(path, "Data", "aims.pkl"), "rb") as f:
+        return pickle.load(f)[0]
+
+
+def backtest_functions():
+    """The function definitions pfml_w / initial_weights_new / compute_stats / pf_ts_fun of PFML_best_hps.py:137-259,
+    exec'd on their own (the script itself imports plotnine, which is not installed)."""
+    GF = _import_general_functions()
+    src = open(os.path.join(REF, "PFML_best_hps.py")).read()
+    a = src.index("def initial_weights_new(")
+    b = src.index("#%% Get best Hyperparameter combination")
+    ns = {"np": np, "pd": pd, "create_cov": GF.create_cov, "create_lambda": GF.create_lambda, "m_func": GF.m_func}
+    seg = src[a:b]
+    # pandas >= 3 drops the grouping column inside groupby().apply(); bring 'eom' back from the group index
+    # (second pandas-compatibility patch besides freq='M' -> 'ME'; the arithmetic is untouched)
+    old = ".reset_index(drop=True)[[\"id\", \"eom\", \"w_start\"]]"
+    assert seg.count(old) == 2
+    seg = seg.replace(old, ".reset_index(level=0).reset_index(drop=True)[[\"id\", \"eom\", \"w_start\"]]")
+    exec(compile(seg, "PFML_best_hps.py[functions]", "exec"), ns)
+    return ns

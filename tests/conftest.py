@@ -33,7 +33,9 @@ def relerr(a, b):
 
 def panel_from_golden(z, syn_mod):
     sc = z["panel_scalars"]
-    return syn_mod.Panel(ids=z["panel_ids"], month_ends=z["panel_month_ends"], feats=z["panel_feats"],
+    feats = z["panel_feats_q"].astype("float64") / 1000.0
+    return syn_mod.Panel(me=z["panel_me"], tr_ld1=z["panel_tr_ld1"], mu_ld1=z["panel_mu_ld1"],
+                         ids=z["panel_ids"], month_ends=z["panel_month_ends"], feats=feats,
                          valid=z["panel_valid"], ret_ld1=z["panel_ret_ld1"], tr_ld0=z["panel_tr_ld0"],
                          mu_ld0=z["panel_mu_ld0"], lam=z["panel_lam"], wealth=z["panel_wealth"], rf=z["panel_rf"],
                          fct_load=z["panel_fct_load"], fct_cov=z["panel_fct_cov"], ivol=z["panel_ivol"],

@@ -88,3 +88,38 @@ def test_ewma_vol_known_answer(funcs):
 def test_feature_index_map_bit_exact(funcs):
     for p in (4, 8, 16):
         assert (O.pfml_feat_idx(p, 16) == funcs[f"feat_idx_{p}"]).all()
+
+
+def _golden_coef(gold):
+    return {int(y): {int(p): gold[f"coef_{y}_{p}"] for p in gold["p_vec"]} for y in gold["years"]}
+
+
+def test_hp_reals_aim_backtest_match_reference(gold, syn):
+    """Next rows: validation utility table, aim portfolio, back-test weights and statistics."""
+    panel = panel_from_golden(gold, syn)
+    hot = [int(t) for t in gold["hot"]]
+    p_vec, l_vec, years = [int(p) for p in gold["p_vec"]], gold["l_vec"], [int(y) for y in gold["years"]]
+    coef = _golden_coef(gold)
+    v = O.hp_reals(gold["r_tilde"], gold["denom"], panel.month_ends[hot], coef, years, p_vec, l_vec)
+    assert (v["l"].to_numpy() == gold["val_l"]).all() and (v["p"].to_numpy() == gold["val_p"]).all()
+    assert (v["eom"].to_numpy().astype("datetime64[D]") == gold["val_eom"]).all()
+    assert relerr(v["obj"].to_numpy(), gold["val_obj"]) < 1e-10
+    assert relerr(v["cum_obj"].to_numpy(), gold["val_cum_obj"]) < 1e-10
+    assert (v["rank"].to_numpy() == gold["val_rank"]).all()
+    oos = [int(t) for t in gold["oos_idx"]]
+    sig = {t: gold["signal_t"][hot.index(t), :int(gold["n_d"][hot.index(t)])] for t in oos}
+    aims = O.aim_portfolios(v, coef, sig, panel.month_ends, oos, None)
+    w_aim = {}
+    for k, t in enumerate(oos):
+        sel = np.flatnonzero(panel.valid[t])
+        assert aims[t][0] == gold["aim_p"][k] and aims[t][1] == gold["aim_l"][k]
+        assert relerr(aims[t][2], gold["w_aim"][k, sel]) < 1e-12
+        w_aim[t] = gold["w_aim"][k, sel]
+    w = O.pfml_w(panel, oos, w_aim)
+    st = O.pf_stats(panel, w)
+    for k, t in enumerate(oos):
+        sel = np.flatnonzero(panel.valid[t])
+        assert relerr(w[t]["w"], gold["bt_w"][k, sel]) < 1e-10
+        assert relerr(w[t]["w_start"], gold["bt_w_start"][k, sel]) < 1e-10
+        assert relerr(np.array([st[t][n] for n in ("inv", "shorting", "turnover", "r", "tc")]), gold["bt_stats"][k]) < 1e-10
+    assert abs(w[oos[0]]["w_start"].sum() - 1.0) < 1e-14            # value-weighted start
