@@ -117,6 +117,32 @@ int pfml_wcov_wcor(const double* fct_ret, const int* end_idx, int n_calc, int K,
  * entries, var_start = sum x^2 / (count - 1), var_i = lam var_{i-1} + (1 - lam) x_{i-1}^2 (NaN carries). */
 int pfml_ewma_vol(const double* x, const long* series_ptr, int n_series, double lam, int start, double* vol, void* stream);
 
+/* f1 -- validation utility of PFML_hp_reals.py:90-102: obj[b][l] = r~_sub' beta - 1/2 beta' denom_sub beta for one p,
+ * with beta [Y][n_l][p+1] (the ridge grid's block of that p) and date_year[b] (device int32) the hp-year index whose
+ * coefficients date b is scored with (-1: not scored, obj = NaN).  `sub` is the pfml_feat_fun(p) index set. */
+int pfml_validation_utility(const double* r_tilde, const double* denom, int B, int p_max, const int* date_year,
+                            const double* beta, int p, int n_l, double* obj, void* stream);
+
+/* f2 -- aim portfolio of PFML_aim_fun.py:150-160: w_aim[b][i] = signal_t[b][i][:] . beta_full[b][:], beta_full [B][P]
+ * being the chosen coefficients scattered into the feat_all layout (zeros outside pfml_feat_fun(p)). */
+int pfml_aim_weights(const double* signal_t, const int* n_sel, int B, int NP, int P, const double* beta_full,
+                     double* w_aim, void* stream);
+
+/* f3 -- m = m_func(...) (General_functions.py:919-962) for B dates straight from the panel's factor form, as
+ * PFML_best_hps.py:186-190 calls it once per out-of-sample month: m_out [B][NP][NP].  The panel needs every field
+ * except rff / vol_scale. */
+size_t pfml_mfunc_dates_workspace_bytes(const pfml_panel_t* panel, int B, int n_max);
+int pfml_mfunc_dates(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                     double* m_out, int* status, void* workspace, size_t workspace_bytes, void* stream);
+
+/* f3 -- the back-test recursion pfml_w (PFML_best_hps.py:168-216) and compute_stats (:220-239) over B consecutive
+ * dates: value-weighted start from me [T*N] at the first date, w = m w_start + (I - m) w_aim, next start =
+ * w (1 + tr_ld1) / (1 + mu_ld1) (tr_ld1 [T*N], mu_ld1 [T]); stocks entering later start at 0.  carry [N] is scratch.
+ * Outputs w_start, w [B][NP] and stats [B][5] = inv, shorting, turnover, r, tc. */
+int pfml_backtest(const pfml_panel_t* panel, const double* me, const double* tr_ld1, const double* mu_ld1, int B, int n_max,
+                  const int* date_t, const int* sel, const int* n_sel, const double* m, const double* w_aim, double* carry,
+                  double* w_start, double* w, double* stats, void* stream);
+
 /* General batched FP64 GEMM on the DMMA pipe, D = alpha * op(A) op(B) + beta * D0 (the reference's `@`):
  * trans_a/trans_b = 0: stored [M][K] / [K][N]; 1: stored transposed.  Batch strides in elements. */
 int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alpha, const double* A, long lda, long sA,

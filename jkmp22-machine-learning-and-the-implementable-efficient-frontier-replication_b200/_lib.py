@@ -70,6 +70,15 @@ SIGNATURES = {
     "pfml_wcov_wcor": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_double,
                                  C.c_void_p, C.c_void_p]),
     "pfml_ewma_vol": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),
+    "pfml_validation_utility": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                          C.c_void_p, C.c_void_p]),
+    "pfml_aim_weights": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "pfml_mfunc_dates_workspace_bytes": (C.c_size_t, [C.POINTER(PanelStruct), C.c_int, C.c_int]),
+    "pfml_mfunc_dates": (C.c_int, [C.POINTER(PanelStruct), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "pfml_backtest": (C.c_int, [C.POINTER(PanelStruct), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                C.c_void_p]),
     "pfml_dgemm_batched": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_void_p, C.c_long, C.c_long, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_int, C.c_void_p]),

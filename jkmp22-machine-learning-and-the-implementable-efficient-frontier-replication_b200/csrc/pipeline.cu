@@ -464,6 +464,66 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// m = Lambda^-1/2 m~ Lambda^1/2 for a batch of dates from the factor form (stage a5 of the date-step alone);
+// used by the back-test, which the reference feeds with one m_func call per month (PFML_best_hps.py:186-190).
+// m_out is [B][NP][NP] (rows / columns >= n_sel[b] belong to the decoupled dummy stocks).
+// ------------------------------------------------------------------------------------------------
+struct MfWs { BatchVecs v; MtBufs m; double *Ut, *Ev, *G; size_t bytes; };
+
+static MfWs carve_mf(void* ws, size_t cap, int B, int NP, int nt, int K) {
+  MfWs w{};
+  Carver c(ws, cap);
+  const size_t BNN = (size_t)B * NP * NP;
+  w.v.sl = c.take<double>((size_t)B * NP); w.v.isl = c.take<double>((size_t)B * NP);
+  w.v.g = c.take<double>((size_t)B * nt * NP); w.v.g0raw = c.take<double>((size_t)B * NP);
+  w.v.rv = c.take<double>((size_t)B * NP); w.v.dvl = c.take<double>((size_t)B * NP);
+  w.v.Lg = c.take<double>((size_t)B * NP * KP); w.v.Lt = c.take<double>((size_t)B * NP * KP);
+  w.v.LF = c.take<double>((size_t)B * NP * KP); w.v.Fg = c.take<double>((size_t)B * KP * KP);
+  w.v.scal = c.take<double>((size_t)B * NSCAL);
+  w.m.x = c.take<double>(BNN); w.m.sgr = c.take<double>(BNN); w.m.yv = c.take<double>((size_t)B * NP);
+  w.m.Mdb = nullptr; w.m.Ya = nullptr; w.m.Yb = nullptr;
+  w.m.Wk = c.take<double>(BNN); w.m.Xinv = c.take<double>(BNN); w.m.T1 = c.take<double>(BNN); w.m.mt = c.take<double>(BNN);
+  w.m.part = c.take<double>((size_t)B * NORM_CHUNKS * 3); w.m.sc = c.take<double>((size_t)B * 8);
+  w.Ut = c.take<double>((size_t)B * NP * KP); w.Ev = c.take<double>((size_t)B * NP);
+  w.G = c.take<double>((size_t)B * NP * stj_ldg(K));
+  w.bytes = c.off;
+  return w;
+}
+
+size_t mtilde_factor_workspace_bytes(const pfml_panel_t* panel, int B, int n_max) {
+  if (!panel || B <= 0 || n_max <= 0) return 0;
+  return carve_mf(nullptr, 0, B, pfml_padded_n(n_max), panel->lb + 2, panel->K).bytes;
+}
+
+int mtilde_factor_for_dates(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                            double* m_out, int* status, void* workspace, size_t workspace_bytes, cudaStream_t s) {
+  if (!panel || B <= 0 || n_max <= 0 || !date_t || !sel || !n_sel || !m_out || !workspace) {
+    set_error("pfml_mfunc_dates: null/empty argument");
+    return -1;
+  }
+  if (panel->K > KP || panel->K <= 0) {
+    set_error("pfml_mfunc_dates: K = %d factors unsupported (1..%d)", panel->K, KP);
+    return -2;
+  }
+  const PanelView pv = view_of(panel);
+  const int NP = pfml_padded_n(n_max);
+  MfWs w = carve_mf(workspace, workspace_bytes, B, NP, pv.lb + 2, pv.K);
+  if (w.bytes > workspace_bytes) {
+    set_error("pfml_mfunc_dates: workspace too small (%zu < %zu bytes)", workspace_bytes, w.bytes);
+    return -3;
+  }
+  if (status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
+  ProfScope ps(T_MFUNC, s);
+  PFML_TRY(prep_vectors(pv, B, NP, date_t, sel, n_sel, w.v, s));
+  PFML_TRY(build_x_factor(pv, B, NP, date_t, sel, n_sel, w.v, w.m.x, w.m.sgr, w.m.yv, s));
+  PFML_TRY(mt0_stieltjes(B, NP, pv.K, n_sel, w.v, w.Ut, w.Ev, w.G, w.m.mt, status, s));
+  double* mt = nullptr;
+  PFML_TRY(fixed_point(B, NP, pv.iterations, w.m, status, s, &mt));
+  PFML_TRY(m_from_mtilde(B, NP, NP, mt, w.v.isl, w.v.sl, m_out, s));
+  return 0;
+}
+
 }  // namespace pfml
 
 // =================================================================================================
