@@ -61,3 +61,45 @@ def validation(r_tilde, denom, month_ends, coef, hp_years, p_vec, l_vec, device=
     v["cum_obj"] = v.groupby(["p", "l"])["obj"].expanding().mean().reset_index(level=[0, 1], drop=True)
     v["rank"] = v.groupby("eom_ret")["cum_obj"].rank(ascending=False, method="dense")
     return v.assign(g=g_index).reset_index(drop=True)
+
+
+def run(path, settings=None, device="cuda:0", strict_reference_bug=False):
+    """PFML_hp_reals.py: reads Data/pfml_input_{g}.pkl and Data/coef_dict_{g}.pkl, writes Data/validation.csv (:130).
+
+    Quirk Q12: the reference initialises ``rows`` outside the g loop (:60 vs :62), so the table of g = 1 also contains
+    the rows of g = 0 relabelled g = 1.  ``strict_reference_bug=True`` reproduces that; the default gives every g its
+    own rows."""
+    import os
+    import pickle
+
+    from . import general_functions as GF
+    settings, _pf = settings or GF.get_settings()
+    hp_years = np.arange(settings["pf"]["dates"]["start_year"], settings["pf"]["dates"]["end_yr"] + 1)
+    p_vec, l_vec = settings["pf_ml"]["p_vec"], settings["pf_ml"]["l_vec"]
+    tables, carried = [], []
+    for g_index, _g in enumerate(settings["pf_ml"]["g_vec"]):
+        with open(os.path.join(path, "Data", f"pfml_input_{g_index}.pkl"), "rb") as f:
+            reals = pickle.load(f)[g_index]["reals"]
+        with open(os.path.join(path, "Data", f"coef_dict_{g_index}.pkl"), "rb") as f:
+            hp_coef = pickle.load(f)[g_index]
+        d_all = sorted(reals.keys())
+        r_t = np.stack([reals[d]["r_tilde"].to_numpy() for d in d_all])
+        den = np.stack([reals[d]["denom"].to_numpy() for d in d_all])
+        me = np.array([np.datetime64(pd.Timestamp(d).date()) for d in d_all])
+        coef = {int(y): {int(p): np.stack([hp_coef[y][p][j].to_numpy() for j in range(len(l_vec))]) for p in p_vec}
+                for y in hp_years}
+        v = validation(r_t, den, me, coef, hp_years, p_vec, l_vec, device=device, g_index=g_index)
+        if strict_reference_bug and carried:
+            raw = pd.concat(carried + [v[["eom", "eom_ret", "obj", "l", "p", "hp_end"]]], ignore_index=True)
+            raw = raw.sort_values(["p", "l", "eom_ret"], kind="stable")
+            raw["cum_obj"] = raw.groupby(["p", "l"])["obj"].expanding().mean().reset_index(level=[0, 1], drop=True)
+            raw["rank"] = raw.groupby("eom_ret")["cum_obj"].rank(ascending=False, method="dense")
+            carried.append(v[["eom", "eom_ret", "obj", "l", "p", "hp_end"]])
+            v = raw.assign(g=g_index)
+        else:
+            carried.append(v[["eom", "eom_ret", "obj", "l", "p", "hp_end"]])
+        tables.append(v)
+    out = pd.concat(tables)
+    out[["eom", "eom_ret", "obj", "l", "p", "hp_end", "cum_obj", "rank", "g"]].to_csv(os.path.join(path, "Data", "validation.csv"),
+                                                                                    index=False)
+    return out

@@ -52,6 +52,39 @@ def test_pfml_input_data_and_search_coef_scripts(tmp_path, syn):
                     assert relerr(s.to_numpy(), ref[j]) < 1e-8, (y, p, l)
 
 
+def test_hp_reals_and_aim_fun_scripts(tmp_path, syn):
+    """validation.csv and aims.pkl written by the drop-ins equal what the exec'd reference scripts wrote."""
+    z = np.load(os.path.join(GOLD, "pfml_ref_small.npz"))
+    panel = panel_from_golden(z, syn)
+    path = str(tmp_path) + "/"
+    syn.write_reference_artefacts(panel, path)
+    GF = pkg("general_functions")
+    settings, pf_set = GF.get_settings()
+    settings["split"]["test_end"] = pd.Timestamp(panel.month_ends[-1])
+    settings["pf"]["dates"].update(start_year=2013, end_yr=2014, split_years=1)
+    settings["pf_ml"].update(g_vec=[panel.meta["g"]], p_vec=[int(p) for p in z["p_vec"]], l_vec=[float(l) for l in z["l_vec"]])
+    st = (settings, pf_set)
+    pkg("pfml_input_data").run(path, st)
+    # score with the reference's own coefficients so that lambda = 0 conditioning does not enter the comparison
+    coef = {0: {int(y): {int(p): {j: pd.Series(z[f"coef_{y}_{p}"][j], index=GF.pfml_feat_fun(int(p))) for j in range(len(z["l_vec"]))}
+                         for p in z["p_vec"]} for y in z["years"]}}
+    with open(os.path.join(path, "Data", "coef_dict_0.pkl"), "wb") as f:
+        pickle.dump(coef, f)
+    v = pkg("pfml_hp_reals").run(path, st)
+    v2 = pd.read_csv(os.path.join(path, "Data", "validation.csv"), parse_dates=["eom", "eom_ret"])
+    assert list(v2.columns) == ["eom", "eom_ret", "obj", "l", "p", "hp_end", "cum_obj", "rank", "g"]
+    assert relerr(v["obj"].to_numpy(), z["val_obj"]) < 1e-8 and (v["rank"].to_numpy() == z["val_rank"]).all()
+    aims = pkg("pfml_aim_fun").run(path, st)[0]
+    dates = sorted(aims.keys())
+    assert [np.datetime64(d.date()) for d in dates] == list(panel.month_ends[z["oos_idx"]])
+    for b, d in enumerate(dates):
+        sel = np.flatnonzero(panel.valid[z["oos_idx"][b]])
+        a = aims[d]["aim_pf"]
+        assert list(a["id"]) == list(panel.ids[sel]) and list(a.columns) == ["id", "eom", "w_aim"]
+        assert relerr(a["w_aim"].to_numpy(), z["w_aim"][b, sel]) < 1e-8
+        assert len(aims[d]["coef"]) == z["aim_p"][b] + 1
+
+
 def test_function_mirrors(syn):
     GF = pkg("general_functions")
     f = np.load(os.path.join(GOLD, "funcs_ref.npz"))
