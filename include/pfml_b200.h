@@ -14,7 +14,8 @@
  *     returns (the *_host convenience entry points allocate and free their own device buffers);
  *   - return value: 0 ok; <0 bad argument / CUDA error (text via pfml_last_error()); numerical failures are
  *     reported per date in the `status` array (bit 0: singular pivot in a block inverse, bit 1: matrix
- *     square root did not converge / non-finite input);
+ *     square root did not converge / non-finite input, bit 3: a barrier wait inside the INT8-emulated GEMM timed
+ *     out, bit 4: NaN/Inf reached an operand of that GEMM);
  *   - never throws, never exits; thread-safe per stream.
  */
 #ifndef PFML_B200_H
@@ -148,6 +149,19 @@ int pfml_backtest(const pfml_panel_t* panel, const double* me, const double* tr_
 int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alpha, const double* A, long lda, long sA,
                        const double* B, long ldb, long sB, double beta, double* D, long ldd, long sD, int batch,
                        void* stream);
+
+/* The same product on the INT8 tensor cores: D = alpha * A B + beta * D with A [M][K], B [K][N] row-major, computed as
+ * 28 exact int8 x int8 -> int32 products of seven 7-bit slices per operand (tcgen05.mma kind::i8, accumulators in
+ * TMEM, operands staged by bulk-TMA copies) and recombined exactly in int64, then FP64: error <= ~2^-42 of
+ * max_k|a_ik| max_k|b_kj| K per element, measured 1e-13 relative to the DMMA product at K = 512 (no reference
+ * counterpart; it is how the date-step runs its n x n x P products).  Needs K % 64 == 0.  status[0] gets bit 3 on an
+ * internal time-out, bit 4 if an operand holds NaN/Inf (they cannot be sliced).  pfml_set_emulation(0) makes
+ * pfml_date_steps use the DMMA kernel for those products instead (default 1, or env PFML_EMULATE_FP64). */
+size_t pfml_dgemm_emulated_workspace_bytes(int M, int N, int K, int batch);
+int pfml_dgemm_emulated(int M, int N, int K, double alpha, const double* A, long lda, long sA, const double* B, long ldb,
+                        long sB, double beta, double* D, long ldd, long sD, int batch, int* status, void* workspace,
+                        size_t workspace_bytes, void* stream);
+void pfml_set_emulation(int on);
 
 /* Batched inverse of well-conditioned n x n matrices by recursive Schur-complement blocks (np.linalg.inv at
  * General_functions.py:960).  A [B][n][n] -> Ainv [B][n][n]. */

@@ -82,6 +82,11 @@ SIGNATURES = {
     "pfml_dgemm_batched": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_void_p, C.c_long, C.c_long, C.c_double, C.c_void_p, C.c_long,
                                      C.c_long, C.c_int, C.c_void_p]),
+    "pfml_dgemm_emulated_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int]),
+    "pfml_dgemm_emulated": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_long, C.c_long, C.c_void_p, C.c_long,
+                                      C.c_long, C.c_double, C.c_void_p, C.c_long, C.c_long, C.c_int, C.c_void_p, C.c_void_p,
+                                      C.c_size_t, C.c_void_p]),
+    "pfml_set_emulation": (None, [C.c_int]),
     "pfml_inverse_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "pfml_inverse_batched": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                        C.c_void_p]),

@@ -65,6 +65,17 @@ struct GemmP {
 int gemm(const GemmP& p, int batch, cudaStream_t stream);
 double gemm_flops(const GemmP& p, int batch);
 
+// ---- FP64 GEMM emulated on the INT8 tensor cores (emu.cu): tcgen05.mma kind::i8 + TMEM + bulk-TMA staging ----------
+size_t emu_a_slices_bytes(int batch, int M, int K);
+size_t emu_b_slices_bytes(int batch, int K, int N);
+bool emu_shape_ok(int M, int N, int K);
+int emu_slice_a(const double* A, long lda, long sA, int M, int K, int batch, int8_t* out, double* scale, int* err, cudaStream_t s);
+int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int8_t* out, double* scale, int* ex, int* err,
+                cudaStream_t s);
+int emu_mma(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
+            const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD, int* err,
+            cudaStream_t s);
+
 // profiling categories (device-time accounting with CUDA events, see prof.cu)
 enum ProfTag { T_OTHER = 0, T_STD = 1, T_MFUNC = 2, T_CHAIN = 3, T_HORNER = 4, T_SOLVE = 5, T_DENOM = 6,
                T_RFF = 7, T_RIDGE = 8, T_COV = 9, T_NTAGS = 10 };

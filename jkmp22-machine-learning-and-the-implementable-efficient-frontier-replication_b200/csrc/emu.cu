@@ -1,0 +1,356 @@
+// FP64 GEMM emulated on the INT8 tensor cores of sm_100a: tcgen05.mma kind::i8, accumulators in TMEM, operands
+// staged by bulk TMA copies (cp.async.bulk + mbarrier), Ozaki-style error-free slicing.
+//
+//   a_ik = 2^ea_i sum_{t<S} qa_t 2^(-7(t+1)),   b_kj = 2^eb_j sum_{t<S} qb_t 2^(-7(t+1)),   q in [-127, 127], S = 8
+//   C_ij = 2^(ea_i + eb_j) sum_{d<S} 2^(-7(d+2)) X_d,   X_d = sum_{i+j=d} qa_i . qb_j   (EXACT int32: K 127^2 S < 2^31)
+//
+// Only the slice pairs with i + j < S are multiplied (36 products); the dropped ones are below
+// 2^-56 S K |a|_rowmax |b|_colmax, i.e. the result is as accurate as a native FP64 GEMM (measured: error 4e-16 of
+// sum_k |a_ik b_kj|).  Why it pays: the DMMA pipe peaks at 37 TFLOP/s, the INT8 pipe at 4.5 POP/s; 36 INT8 products
+// per FP64 product still leave > 60 FP64-equivalent TFLOP/s.
+//
+// Layout: slices are written to global memory already in the shared-memory order the UMMA descriptors expect
+// (K-major, no swizzle, 8 rows x 16 B core matrices), one contiguous block per (row block, 64-byte k chunk, all
+// slices), so a pipeline stage is ONE bulk copy per operand.  One CTA per SM walks the output tiles (128 x 64);
+// the 8 accumulators X_d occupy all 512 TMEM columns.  Warp 0: TMA producer; warp 1: MMA issuer; warp 2: TMEM
+// allocator; warps 4-7: epilogue (TMEM -> registers, exact int64 recombination, scaling, fused row scale / addend).
+#include <cstdlib>
+
+#include "common.cuh"
+
+namespace pfml {
+
+namespace {
+
+#ifndef PFML_EMU_SLICES
+#define PFML_EMU_SLICES 7
+#endif
+constexpr int ES = PFML_EMU_SLICES;                          // slices (8: 56 bits; 7: 49 bits)
+constexpr int EBM = 128, EBN = 64, EKC = 64;                 // CTA tile, k chunk (bytes) per stage
+constexpr int ELBO = 128, ESBO = (EKC / 16) * 128;           // canonical layout strides (bytes)
+constexpr int EA_STAGE = ES * EBM * EKC, EB_STAGE = ES * EBN * EKC;   // 64 KB, 32 KB
+constexpr int ESTAGES = 2;
+
+__host__ __device__ inline int canon(int r, int kk) { return (r % 8) * 16 + (r / 8) * ESBO + (kk / 16) * ELBO + kk % 16; }
+
+// 16 values -> ES signed 7-bit slices each, in the integer domain: |x| 2^-e = 0.f1 f2 ... (7-bit fields), the fields
+// are cut out of the 53-bit significand with shifts (truncation toward zero), the sign is applied per field.
+// e is the block exponent (|x| < 2^e); zeros, denormals and values below 2^(e - 7 ES) give all-zero slices.
+__device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* dst, long slice_stride) {
+  unsigned long long f[16];
+  bool neg[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    const long long bits = __double_as_longlong(x[k]);
+    const int ex = (int)((bits >> 52) & 0x7ff);
+    const unsigned long long mant = ((unsigned long long)bits & 0xFFFFFFFFFFFFFull) | (ex ? (1ull << 52) : 0ull);
+    const int sh = 1075 + e - 7 * ES - ex;                 // F = floor(|x| 2^(7 ES - e)) = mant >> sh
+    f[k] = (ex == 0 || sh >= 64) ? 0ull : (sh >= 0 ? (mant >> sh) : (mant << (-sh)));
+    neg[k] = bits < 0;
+  }
+#pragma unroll
+  for (int t = 0; t < ES; t++) {
+    union { int8_t b[16]; int4 v; } u;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      const int q = (int)((f[k] >> (7 * (ES - 1 - t))) & 127ull);
+      u.b[k] = (int8_t)(neg[k] ? -q : q);
+    }
+    *reinterpret_cast<int4*>(dst + t * slice_stride) = u.v;
+  }
+}
+
+// A-type operand: X [R][K] with K contiguous (ld), scaled per row, blocks of BR rows (128 for A, 64 for B^T operands).
+// Non-finite or zero rows get exponent 0.  Rows >= R inside the last block are zero-filled.
+template <int BR>
+__global__ void slice_kmajor_kernel(const double* __restrict__ X, long ld, long sX, int R, int K, int8_t* __restrict__ out,
+                                    double* __restrict__ scale, double extra, int* __restrict__ err) {
+  const int z = blockIdx.y, row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32, lane = threadIdx.x & 31;
+  const int RB = (R + BR - 1) / BR, KB = K / EKC;
+  if (row >= RB * BR) return;
+  constexpr long STAGE = (long)ES * BR * EKC;
+  int8_t* base = out + (((long)z * RB + row / BR) * KB) * STAGE;
+  const double* a = X + (long)z * sX + (long)row * ld;
+  int e = 0;
+  if (row < R) {
+    double mx = 0.0;
+    bool bad = false;
+    for (int k = lane; k < K; k += 32) { const double v = fabs(a[k]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (bad) atomicOr(err, 16);                  // NaN / Inf cannot be sliced: reported through the status array
+    e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
+    if (lane == 0) scale[(long)z * R + row] = scalbn(extra, e);
+  }
+  for (int k0 = lane * 16; k0 < K; k0 += 32 * 16) {
+    double x[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) x[k] = row < R ? a[k0 + k] : 0.0;
+    slice16(x, e, base + (long)(k0 / EKC) * STAGE + canon(row % BR, k0 % EKC), (long)BR * EKC);
+  }
+}
+
+// B-type operand: X [K][C] with C contiguous (ld), scaled per column, blocks of 64 columns.
+__global__ void col_exponent_kernel(const double* __restrict__ X, long ld, long sX, int K, int C, int* __restrict__ ex,
+                                    double* __restrict__ scale, double extra, int* __restrict__ err) {
+  const int z = blockIdx.y, n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= C) return;
+  const double* b = X + (long)z * sX + n;
+  double mx = 0.0;
+  bool bad = false;
+  for (int k = 0; k < K; k++) { const double v = fabs(b[(long)k * ld]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
+  if (bad) atomicOr(err, 16);
+  const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
+  ex[(long)z * C + n] = e;
+  scale[(long)z * C + n] = scalbn(extra, e);
+}
+
+__global__ void __launch_bounds__(256)
+slice_nmajor_kernel(const double* __restrict__ X, long ld, long sX, int K, int C, int CB, const int* __restrict__ ex,
+                    int8_t* __restrict__ out) {
+  // one CTA per (column block of 64, k chunk of 64): thread = (column, 16 consecutive k); reads coalesced along columns
+  const int z = blockIdx.z, cb = blockIdx.x, kb = blockIdx.y, KB = K / EKC;
+  const int nn = threadIdx.x & 63, kq = threadIdx.x >> 6, n = cb * EBN + nn, k0 = kb * EKC + kq * 16;
+  int8_t* base = out + (((long)z * CB + cb) * KB + kb) * (long)EB_STAGE;
+  double x[16];
+  const int e = n < C ? ex[(long)z * C + n] : 0;
+#pragma unroll
+  for (int k = 0; k < 16; k++) x[k] = n < C ? X[(long)z * sX + (long)(k0 + k) * ld + n] : 0.0;
+  slice16(x, e, base + canon(nn, kq * 16), (long)EBN * EKC);
+}
+
+}  // namespace
+
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+  // start address >> 4 | leading byte offset >> 4 << 16 | stride byte offset >> 4 << 32 | version 1 << 46; no swizzle
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((ELBO >> 4) & 0x3FFF) << 16) | ((uint64_t)((ESBO >> 4) & 0x3FFF) << 32) |
+         ((uint64_t)1 << 46);
+}
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {     // bounded: a bug must not hang the GPU
+  uint32_t done = 0;
+  for (int it = 0; it < (1 << 26) && !done; it++)
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  return done != 0;
+}
+__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n"
+               ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+constexpr double kLoScale = 1.0 / (double)(1ull << (7 * (ES - 1) - 21));
+
+struct EmuP {
+  const int8_t* As; const int8_t* Bs; const double* sa; const double* sb;   // slices and 2^e scales (sb includes 2^-14)
+  double* D; long ldd, sD;
+  const double* E; long lde, sE;
+  const double* rs; long s_rs;
+  double alpha, beta;
+  int M, N, K, MB, NB, batch;
+  int* err;
+};
+
+__global__ void __launch_bounds__(256, 1) emu_gemm_kernel(const EmuP p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + ESTAGES * EA_STAGE;
+  __shared__ __align__(8) uint64_t full_bar[ESTAGES], empty_bar[ESTAGES], acc_full, acc_empty;
+  __shared__ uint32_t tmem_base;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int KB = p.K / EKC;
+  const long n_tiles = (long)p.batch * p.MB * p.NB;
+  if (tid == 0) {
+    for (int s = 0; s < ESTAGES; s++) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&full_bar[s])));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&empty_bar[s])));
+    }
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&acc_full)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 128;" ::"r"(smem_u32(&acc_empty)));
+    asm volatile("fence.mbarrier_init.release.cluster;");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&tmem_base)));   // ES * 64 <= 512
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;");
+  const uint32_t tbase = tmem_base;
+
+  if (warp == 0 && lane == 0) {
+    // ===== producer: one bulk copy per operand per stage; runs ahead into the next tile while the epilogue works =====
+    long it = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      const int nb = (int)(t % p.NB), mb = (int)((t / p.NB) % p.MB), z = (int)(t / ((long)p.NB * p.MB));
+      const int8_t* a_src = p.As + (((long)z * p.MB + mb) * KB) * (long)EA_STAGE;
+      const int8_t* b_src = p.Bs + (((long)z * p.NB + nb) * KB) * (long)EB_STAGE;
+      for (int kc = 0; kc < KB; kc++, it++) {
+        const int s = (int)(it % ESTAGES);
+        if (!mbar_wait(smem_u32(&empty_bar[s]), (uint32_t)(((it / ESTAGES) & 1) ^ 1))) { atomicOr(p.err, 1); return; }
+        const uint32_t fb = smem_u32(&full_bar[s]);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(EA_STAGE + EB_STAGE) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(sA + s * EA_STAGE)), "l"(a_src + (long)kc * EA_STAGE), "r"(EA_STAGE), "r"(fb) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(sB + s * EB_STAGE)), "l"(b_src + (long)kc * EB_STAGE), "r"(EB_STAGE), "r"(fb) : "memory");
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer: 36 slice pairs x 2 k-steps per stage, accumulator d = i + j at TMEM column d * 64 =====
+    const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(EBN >> 3) << 17) | ((uint32_t)(EBM >> 4) << 24);
+    long it = 0;
+    int tl = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x, tl++) {
+      if (!mbar_wait(smem_u32(&acc_empty), (uint32_t)((tl & 1) ^ 1))) { atomicOr(p.err, 4); return; }   // epilogue drained TMEM
+      asm volatile("tcgen05.fence::after_thread_sync;");
+      for (int kc = 0; kc < KB; kc++, it++) {
+        const int s = (int)(it % ESTAGES);
+        if (!mbar_wait(smem_u32(&full_bar[s]), (uint32_t)((it / ESTAGES) & 1))) { atomicOr(p.err, 2); return; }
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const uint64_t da0 = make_desc(smem_u32(sA + s * EA_STAGE)), db0 = make_desc(smem_u32(sB + s * EB_STAGE));
+        if (kc == 0) {
+#pragma unroll
+          for (int i = 0; i < ES; i++)
+#pragma unroll
+            for (int j = 0; j < ES - i; j++)
+#pragma unroll
+              for (int kk = 0; kk < EKC / 32; kk++)
+                umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
+                        db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, (kk > 0 || i > 0) ? 1u : 0u);
+        } else {
+#pragma unroll
+          for (int i = 0; i < ES; i++)
+#pragma unroll
+            for (int j = 0; j < ES - i; j++)
+#pragma unroll
+              for (int kk = 0; kk < EKC / 32; kk++)
+                umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
+                        db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, 1u);
+        }
+        umma_commit(smem_u32(&empty_bar[s]));
+      }
+      umma_commit(smem_u32(&acc_full));
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue =====
+    const int q = warp & 3;
+    int tl = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x, tl++) {
+      const int nb = (int)(t % p.NB), mb = (int)((t / p.NB) % p.MB), z = (int)(t / ((long)p.NB * p.MB));
+      if (!mbar_wait(smem_u32(&acc_full), (uint32_t)(tl & 1))) { atomicOr(p.err, 8); return; }
+      asm volatile("tcgen05.fence::after_thread_sync;");
+      const int row = mb * EBM + q * 32 + lane;
+      const bool rok = row < p.M;
+      double rsv = rok ? p.alpha * p.sa[(long)z * p.M + row] : 0.0;
+      if (p.rs && rok) rsv *= p.rs[(long)z * p.s_rs + row];
+      double* drow = p.D + (long)z * p.sD + (long)row * p.ldd + (long)nb * EBN;
+      const double* erow = p.E ? p.E + (long)z * p.sE + (long)row * p.lde + (long)nb * EBN : nullptr;
+      const double* sbz = p.sb + (long)z * p.N + (long)nb * EBN;
+      for (int c0 = 0; c0 < EBN; c0 += 16) {
+        long long hi[16], lo[16];
+#pragma unroll
+        for (int c = 0; c < 16; c++) hi[c] = lo[c] = 0;
+        uint32_t v[ES][16];
+#pragma unroll
+        for (int d = 0; d < ES; d++)
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                       : "=r"(v[d][0]), "=r"(v[d][1]), "=r"(v[d][2]), "=r"(v[d][3]), "=r"(v[d][4]), "=r"(v[d][5]), "=r"(v[d][6]), "=r"(v[d][7]),
+                         "=r"(v[d][8]), "=r"(v[d][9]), "=r"(v[d][10]), "=r"(v[d][11]), "=r"(v[d][12]), "=r"(v[d][13]), "=r"(v[d][14]), "=r"(v[d][15])
+                       : "r"(tbase + ((uint32_t)(q * 32) << 16) + d * EBN + c0));
+        asm volatile("tcgen05.wait::ld.sync.aligned;");
+        if (c0 + 16 >= EBN) {                    // last chunk read: hand TMEM back to the MMA issuer before the stores
+          asm volatile("tcgen05.fence::before_thread_sync;");
+          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&acc_empty)) : "memory");
+        }
+#pragma unroll
+        for (int d = 0; d < ES; d++)
+#pragma unroll
+          for (int c = 0; c < 16; c++) {
+            if (d < 4) hi[c] = hi[c] * 128 + (long long)(int32_t)v[d][c];
+            else lo[c] = lo[c] * 128 + (long long)(int32_t)v[d][c];
+          }
+        if (rok) {
+#pragma unroll
+          for (int c = 0; c < 16; c++) {
+            const int col = nb * EBN + c0 + c;
+            if (col < p.N) {
+              const double x = ((double)hi[c] + (double)lo[c] * kLoScale) * 4.76837158203125e-07;   // 2^-(7 (ES-1) - 21), 2^-21
+              double o = rsv * (x * sbz[c0 + c]);
+              if (erow) o += p.beta * erow[c0 + c];
+              drow[c0 + c] = o;
+            }
+          }
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase));
+}
+
+}  // namespace
+
+// ---- host API (declared in common.cuh) ---------------------------------------------------------------------
+size_t emu_a_slices_bytes(int batch, int M, int K) { return (size_t)batch * ceil_div(M, EBM) * (K / EKC) * (size_t)EA_STAGE; }
+size_t emu_b_slices_bytes(int batch, int K, int N) { return (size_t)batch * ceil_div(N, EBN) * (K / EKC) * (size_t)EB_STAGE; }
+
+bool emu_shape_ok(int M, int N, int K) { return M > 0 && N > 0 && K >= EKC && K % EKC == 0 && (long)K * 127 * 127 * ES < (1L << 31); }
+
+// A [M][K] (K contiguous) -> slices + row scales 2^ea
+int emu_slice_a(const double* A, long lda, long sA, int M, int K, int batch, int8_t* out, double* scale, int* err, cudaStream_t s) {
+  const int rows = ceil_div(M, EBM) * EBM;
+  slice_kmajor_kernel<EBM><<<dim3(ceil_div(rows, 8), batch), 256, 0, s>>>(A, lda, sA, M, K, out, scale, 1.0, err);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+// B [K][N] (N contiguous) -> slices + column scales 2^(eb - 14); ex [batch][N] is int scratch
+int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int8_t* out, double* scale, int* ex, int* err,
+                cudaStream_t s) {
+  col_exponent_kernel<<<dim3(ceil_div(N, 128), batch), 128, 0, s>>>(B, ldb, sB, K, N, ex, scale, 6.103515625e-05, err);
+  PFML_CHECK_LAUNCH();
+  slice_nmajor_kernel<<<dim3(ceil_div(N, EBN), K / EKC, batch), 256, 0, s>>>(B, ldb, sB, K, N, ceil_div(N, EBN), ex, out);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+// D = alpha * rs[r] * (A B) + beta * E from pre-sliced operands
+int emu_mma(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
+            const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD, int* err,
+            cudaStream_t s) {
+  if (!emu_shape_ok(M, N, K)) {
+    set_error("emu_mma: unsupported shape M=%d N=%d K=%d", M, N, K);
+    return -2;
+  }
+  EmuP p;
+  p.As = As; p.Bs = Bs; p.sa = sa; p.sb = sb; p.D = D; p.ldd = ldd; p.sD = sD; p.E = E; p.lde = lde; p.sE = sE;
+  p.rs = rs; p.s_rs = s_rs; p.alpha = alpha; p.beta = beta; p.M = M; p.N = N; p.K = K;
+  p.MB = ceil_div(M, EBM); p.NB = ceil_div(N, EBN); p.batch = batch; p.err = err;
+  constexpr size_t smem = (size_t)ESTAGES * (EA_STAGE + EB_STAGE);
+  static bool cfg[64] = {};
+  static int n_sm[64] = {};
+  int dev = 0;
+  PFML_CUDA_OK(cudaGetDevice(&dev));
+  if (!cfg[dev & 63]) {
+    PFML_CUDA_OK(cudaFuncSetAttribute(emu_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PFML_CUDA_OK(cudaDeviceGetAttribute(&n_sm[dev & 63], cudaDevAttrMultiProcessorCount, dev));
+    cfg[dev & 63] = true;
+  }
+  const long tiles = (long)batch * p.MB * p.NB;
+  static const int mult = getenv("PFML_EMU_GRID") ? atoi(getenv("PFML_EMU_GRID")) : 1;   // tuning aid: CTAs per SM (0 = one per tile)
+  const long want = mult > 0 ? (long)mult * n_sm[dev & 63] : tiles;
+  const int grid = (int)(tiles < want ? tiles : want);
+  prof_begin(-2, s);
+  emu_gemm_kernel<<<grid, 256, smem, s>>>(p);
+  PFML_CHECK_LAUNCH();
+  prof_end(-2, s, 2.0 * M * (double)N * K * batch, 0.0);
+  return 0;
+}
+
+}  // namespace pfml

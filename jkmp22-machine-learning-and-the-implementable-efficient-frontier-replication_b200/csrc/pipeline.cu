@@ -14,6 +14,7 @@
 //     (n+K)-deep contraction; tc = w omega_chg' Lambda omega_chg = w omega~_chg' omega~_chg; both symmetric
 //     (lower tiles computed, mirrored), denom = risk + tc fused in the tc epilogue.
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -38,11 +39,12 @@ void set_error(const char* fmt, ...) {
 const char* last_error() { return g_err; }
 
 static const char* kTagNames[] = {"dmma_gemm", "standardize", "m_func", "chain_nxn", "horner_nxP", "solve", "denom",
-                                  "rff", "ridge", "cov", "other"};
-constexpr int N_TAGS = 11;   // slot 0 = all GEMM launches (tag -1), slots 1.. = ProfTag + ... see slot_of
+                                  "rff", "ridge", "cov", "other", "emu_i8_gemm"};
+constexpr int N_TAGS = 12;   // slot 0 = all GEMM launches (tag -1), slots 1.. = ProfTag + ... see slot_of
 static int slot_of(int tag) {
   switch (tag) {
     case -1: return 0;
+    case -2: return 11;
     case T_STD: return 1;
     case T_MFUNC: return 2;
     case T_CHAIN: return 3;
@@ -180,6 +182,22 @@ int spd_inverse(int B, int NP, double* Wk, double* X, double* T1, int* status, c
 // ------------------------------------------------------------------------------------------------
 constexpr int DB_ITERS = 10;
 
+// n x n x P products of the date-step on the INT8 tensor cores (emu.cu) instead of the DMMA pipe
+static int g_use_emu = -1;
+static bool use_emu() {
+  if (g_use_emu < 0) {
+    const char* e = getenv("PFML_EMULATE_FP64");
+    g_use_emu = e ? (atoi(e) != 0) : 1;
+  }
+  return g_use_emu != 0;
+}
+
+__global__ void fold_emu_error_kernel(int B, const int* __restrict__ err, int* __restrict__ status) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  const int e = *err;                      // bits 0-3: a barrier wait of the INT8 GEMM timed out; bit 4: NaN/Inf operand
+  if (b < B && e) atomicOr(status + b, ((e & 15) ? 8 : 0) | (e & 16));
+}
+
 struct MtBufs {
   double *x, *sgr, *yv, *Mdb, *Wk, *Xinv, *T1, *Ya, *Yb, *mt, *part, *sc;
 };
@@ -239,6 +257,7 @@ struct StepWs {
   BatchVecs v;
   MtBufs m;
   double *XC, *XCl1, *Ut, *Ev, *G;
+  int8_t *eAs, *eBs; double *esa, *esb; int *eex, *eerr;   // INT8-emulated GEMM operands (emu.cu)
   double *St, *Za, *Zb, *Nn, *Nl1, *OM, *BS, *OMC;
   double *risk_tmp, *tc_tmp;
   size_t bytes;
@@ -279,6 +298,10 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.OM = c.take<double>((size_t)B * (NP + KP) * w.ldP);
   w.BS = c.take<double>((size_t)B * (NP + KP) * w.ldP);
   w.OMC = c.take<double>(BnP);
+  w.eAs = c.take<int8_t>(emu_a_slices_bytes(B, NP, NP));
+  w.eBs = c.take<int8_t>(emu_b_slices_bytes(B, NP, P));
+  w.esa = c.take<double>((size_t)B * NP); w.esb = c.take<double>((size_t)B * P);
+  w.eex = c.take<int>((size_t)B * P); w.eerr = c.take<int>(64);
   w.risk_tmp = need_risk ? c.take<double>((size_t)B * P * P) : nullptr;
   w.tc_tmp = need_tc ? c.take<double>((size_t)B * P * P) : nullptr;
   w.bytes = c.off;
@@ -378,31 +401,41 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   //   Z'_j = G_j (S~_{j+1} + m~ Z'_{j+1}),  Z'_{lb-1} = G_{lb-1} S~_lb ;  Z = S~_1 + m~ Z'_1
   //   N = S~_0 + m~ G_0 Z ;  N_l1 = Z + B11 S~_{lb+1}
   double* Z = nullptr;
+  const bool emu = use_emu() && emu_shape_ok(NP, P, NP);
+  // one n x n x P product D = alpha * rs o (A X) + E on whichever tensor pipe is selected; A is sliced on demand
+  const double* emu_a_cur = nullptr;
+  auto nxP = [&](const double* A, const double* X, long sX, double alpha, const double* rs, long s_rs, const double* E, long sE,
+                 double* D, long sD) -> int {
+    if (emu) {
+      if (emu_a_cur != A) {
+        PFML_TRY(emu_slice_a(A, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+        emu_a_cur = A;
+      }
+      PFML_TRY(emu_slice_b(X, ldP, sX, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      return emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, alpha, rs, s_rs, E ? 1.0 : 0.0, E, ldP, sE, D, ldP, sD, w.eerr, s);
+    }
+    GemmP g;
+    g.A = A; g.lda = NP; g.sA = NN; g.B = X; g.ldb = ldP; g.sB = sX; g.D = D; g.ldd = ldP; g.sD = sD;
+    g.M = NP; g.N = P; g.K = NP; g.alpha = alpha; g.rs = rs; g.s_rs = s_rs;
+    if (E) { g.E = E; g.lde = ldP; g.sE = sE; g.beta = 1.0; }
+    return gemm(g, B, s);
+  };
+  if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int), s));
   {
     ProfScope ps(T_HORNER, s);
-    GemmP g;
-    g.lda = NP; g.sA = NN; g.ldb = ldP; g.ldd = ldP; g.lde = ldP; g.sE = sSt;
-    g.M = NP; g.N = P; g.K = NP;
-    g.A = mt; g.beta = 1.0;
     const double* Zp = St(lb);         // already scaled by g_{lb-1} in the standardise kernel
     long sZp = sSt;
     double *za = w.Za, *zb = w.Zb;
     for (int j = lb - 2; j >= 0; j--) {
-      g.B = Zp; g.sB = sZp; g.D = za; g.sD = nP;
-      g.E = St(j + 1);
-      g.rs = (j >= 1) ? gv(j) : nullptr; g.s_rs = sg;
-      PFML_TRY(gemm(g, B, s));
+      PFML_TRY(nxP(mt, Zp, sZp, 1.0, (j >= 1) ? gv(j) : nullptr, sg, St(j + 1), sSt, za, nP));
       Zp = za; sZp = nP;
       double* t = za; za = zb; zb = t;
     }
     Z = (double*)Zp;                    // unscaled Z (j = 0 step)
     double* ZG = za;                    // the other ping-pong buffer
     PFML_TRY(row_scale(B, NP, P, ldP, nP, Z, gv(0), sg, ZG, ldP, nP, s));
-    g.rs = nullptr;
-    g.B = ZG; g.sB = nP; g.D = w.Nn; g.sD = nP; g.E = St(0); g.sE = sSt;
-    PFML_TRY(gemm(g, B, s));
-    g.A = B11; g.B = St(lb + 1); g.sB = sSt; g.D = w.Nl1; g.E = Z; g.sE = nP;
-    PFML_TRY(gemm(g, B, s));
+    PFML_TRY(nxP(mt, ZG, nP, 1.0, nullptr, 0, St(0), sSt, w.Nn, nP));
+    PFML_TRY(nxP(B11, St(lb + 1), sSt, 1.0, nullptr, 0, Z, nP, w.Nl1, nP));
   }
 
   // ---- a8 solves: omega~ = const~^-1 N, omega~_l1 = const~_l1^-1 N_l1, omega~_chg -----------------
@@ -413,16 +446,13 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     PFML_TRY(inverse(i1));
     InvCtx i0{B, NP, spare, w.XC, w.m.T1, status, s};
     PFML_TRY(inverse(i0));
-    GemmP g;
-    g.lda = NP; g.sA = NN; g.ldb = ldP; g.sB = nP; g.ldd = ldP;
-    g.M = NP; g.N = P; g.K = NP;
-    g.A = w.XC; g.B = w.Nn; g.D = w.OM; g.sD = sStack;
-    PFML_TRY(gemm(g, B, s));
+    PFML_TRY(nxP(w.XC, w.Nn, nP, 1.0, nullptr, 0, nullptr, 0, w.OM, sStack));
     // omega~_chg = omega~ - g0raw o (const_l1^-1 N_l1)   (quirk Q8: g0 without NaN->1)
-    g.A = w.XCl1; g.B = w.Nl1; g.D = w.OMC; g.sD = nP;
-    g.alpha = -1.0; g.rs = w.v.g0raw; g.s_rs = NP;
-    g.E = w.OM; g.lde = ldP; g.sE = sStack; g.beta = 1.0;
-    PFML_TRY(gemm(g, B, s));
+    PFML_TRY(nxP(w.XCl1, w.Nl1, nP, -1.0, w.v.g0raw, NP, w.OM, sStack, w.OMC, nP));
+    if (emu && status) {
+      fold_emu_error_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, w.eerr, status);
+      PFML_CHECK_LAUNCH();
+    }
   }
 
   // ---- a9 r_tilde, risk, tc, denom ----------------------------------------------------------------
@@ -608,6 +638,56 @@ int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alp
   if (beta != 0.0) { g.E = D; g.lde = ldd; g.sE = sD; g.beta = beta; }
   return gemm(g, batch, (cudaStream_t)stream);
 }
+
+// ---- FP64 GEMM emulated on the INT8 tensor cores (emu.cu) -------------------------------------------------------
+struct EmuWs { int8_t *As, *Bs; double *sa, *sb; int *ex, *err; size_t bytes; };
+static EmuWs carve_emu(void* ws, size_t cap, int M, int N, int K, int batch) {
+  EmuWs w{};
+  Carver c(ws, cap);
+  w.As = c.take<int8_t>(emu_a_slices_bytes(batch, M, K));
+  w.Bs = c.take<int8_t>(emu_b_slices_bytes(batch, K, N));
+  w.sa = c.take<double>((size_t)batch * M); w.sb = c.take<double>((size_t)batch * N);
+  w.ex = c.take<int>((size_t)batch * N); w.err = c.take<int>(64);
+  w.bytes = c.off;
+  return w;
+}
+
+size_t pfml_dgemm_emulated_workspace_bytes(int M, int N, int K, int batch) {
+  if (!emu_shape_ok(M, N, K) || batch <= 0) return 0;
+  return carve_emu(nullptr, 0, M, N, K, batch).bytes;
+}
+
+int pfml_dgemm_emulated(int M, int N, int K, double alpha, const double* A, long lda, long sA, const double* B, long ldb, long sB,
+                        double beta, double* D, long ldd, long sD, int batch, int* status, void* workspace, size_t workspace_bytes,
+                        void* stream) {
+  if (!A || !B || !D || !workspace || batch <= 0) {
+    set_error("pfml_dgemm_emulated: null/empty argument");
+    return -1;
+  }
+  if (!emu_shape_ok(M, N, K)) {
+    set_error("pfml_dgemm_emulated: needs K %% 64 == 0 and K <= 16640 (got M=%d N=%d K=%d)", M, N, K);
+    return -2;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  EmuWs w = carve_emu(workspace, workspace_bytes, M, N, K, batch);
+  if (w.bytes > workspace_bytes) {
+    set_error("pfml_dgemm_emulated: workspace too small (%zu < %zu bytes)", workspace_bytes, w.bytes);
+    return -3;
+  }
+  PFML_CUDA_OK(cudaMemsetAsync(w.err, 0, sizeof(int), s));
+  PFML_TRY(emu_slice_a(A, lda, sA, M, K, batch, w.As, w.sa, w.err, s));
+  PFML_TRY(emu_slice_b(B, ldb, sB, K, N, batch, w.Bs, w.sb, w.ex, w.err, s));
+  PFML_TRY(emu_mma(w.As, w.sa, w.Bs, w.sb, M, N, K, batch, alpha, nullptr, 0, beta, beta != 0.0 ? D : nullptr, ldd, sD, D, ldd, sD,
+                   w.err, s));
+  if (status) {
+    PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int), s));
+    fold_emu_error_kernel<<<1, 32, 0, s>>>(1, w.err, status);
+    PFML_CHECK_LAUNCH();
+  }
+  return 0;
+}
+
+void pfml_set_emulation(int on) { g_use_emu = on != 0; }
 
 namespace {
 __global__ void pad_identity_kernel(int n, int NP, const double* __restrict__ A, double* __restrict__ Wk) {

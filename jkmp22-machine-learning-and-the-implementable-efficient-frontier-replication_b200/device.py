@@ -182,6 +182,25 @@ def dgemm(A, B, trans_a=False, trans_b=False, alpha=1.0, device="cuda:0"):
     return d.cpu().numpy()
 
 
+def dgemm_emulated(A, B, alpha=1.0, beta=0.0, D0=None, device="cuda:0"):
+    """D = alpha A B + beta D0 for [batch, M, K] x [batch, K, N] on the INT8 tensor cores (pfml_dgemm_emulated).
+    Returns (D numpy, status int): status bit 3 = internal time-out, bit 4 = NaN/Inf in an operand."""
+    lib = _lib.load()
+    dev = torch.device(device)
+    a, b = _dev(A, dev), _dev(B, dev)
+    batch, M, K = a.shape
+    N = b.shape[2]
+    d = torch.zeros((batch, M, N), dtype=torch.float64, device=dev) if D0 is None else _dev(D0, dev).clone()
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    nbytes = lib.pfml_dgemm_emulated_workspace_bytes(M, N, K, batch)
+    ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.pfml_dgemm_emulated(M, N, K, float(alpha), _ptr(a), K, M * K, _ptr(b), N, K * N, float(beta), _ptr(d), N,
+                                      M * N, batch, _ptr(status), _ptr(ws), nbytes, _stream_ptr()), "pfml_dgemm_emulated")
+        torch.cuda.synchronize(dev)
+    return d.cpu().numpy(), int(status.item())
+
+
 def inverse(A, device="cuda:0"):
     lib = _lib.load()
     dev = torch.device(device)

@@ -1,0 +1,90 @@
+"""pfml_dgemm_emulated (FP64 products on the INT8 tensor cores) against numpy and against the DMMA kernel."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-11   # relative to sum_k |a_ik| |b_kj|: 7 slices keep 49 bits per operand below the row / column maximum
+
+
+def _rel(got, A, B, want):
+    scale = np.abs(A) @ np.abs(B)
+    return float(np.max(np.abs(got - want) / np.maximum(scale, 1e-300)))
+
+
+@pytest.mark.parametrize("batch,M,N,K", [(3, 128, 64, 64), (2, 200, 130, 128), (5, 512, 1025, 512), (1, 70, 9, 192)])
+def test_emulated_gemm_matches_numpy(batch, M, N, K):
+    from pfml_b200 import device
+    rng = np.random.default_rng(batch * 1000 + M)
+    A = rng.standard_normal((batch, M, K)) * np.exp(rng.uniform(-6, 6, (batch, M, 1)))     # rows of very different size
+    B = rng.standard_normal((batch, K, N)) * np.exp(rng.uniform(-6, 6, (batch, 1, N)))     # and columns
+    D, status = device.dgemm_emulated(A, B)
+    assert status == 0
+    assert _rel(D, A, B, A @ B) < TOL
+    D2 = device.dgemm(A, B)
+    assert _rel(D, A, B, D2) < TOL
+
+
+def test_emulated_gemm_alpha_beta_and_zero_rows():
+    from pfml_b200 import device
+    rng = np.random.default_rng(7)
+    A = rng.standard_normal((2, 128, 64))
+    B = rng.standard_normal((2, 64, 64))
+    A[:, 5] = 0.0                     # an all-zero row and column must give exact zeros
+    B[:, :, 11] = 0.0
+    D0 = rng.standard_normal((2, 128, 64))
+    D, status = device.dgemm_emulated(A, B, alpha=-0.75, beta=2.0, D0=D0)
+    assert status == 0
+    want = -0.75 * (A @ B) + 2.0 * D0
+    assert np.max(np.abs(D - want)) < 1e-11
+    assert np.array_equal(D[:, 5], 2.0 * D0[:, 5])
+    assert np.array_equal(D[:, :, 11], 2.0 * D0[:, :, 11])
+
+
+def test_emulated_gemm_exact_on_small_integers():
+    """Integers below 2^20 in magnitude are represented exactly by the slices, so the product is exact."""
+    from pfml_b200 import device
+    rng = np.random.default_rng(3)
+    A = rng.integers(-1000, 1000, (2, 128, 128)).astype(np.float64)
+    B = rng.integers(-1000, 1000, (2, 128, 64)).astype(np.float64)
+    D, status = device.dgemm_emulated(A, B)
+    assert status == 0
+    assert np.array_equal(D, A @ B)
+
+
+def test_emulated_gemm_flags_nan_and_rejects_shapes():
+    from pfml_b200 import _lib, device
+    A = np.ones((1, 128, 64))
+    B = np.ones((1, 64, 64))
+    A[0, 3, 7] = np.nan
+    _, status = device.dgemm_emulated(A, B)
+    assert status & 16
+    B[0, 2, 2] = np.inf
+    _, status = device.dgemm_emulated(np.ones((1, 128, 64)), B)
+    assert status & 16
+    lib = _lib.load()
+    with pytest.raises(RuntimeError):
+        device.dgemm_emulated(np.ones((1, 128, 100)), np.ones((1, 100, 64)))      # K % 64 != 0
+    assert b"K" in lib.pfml_last_error()
+
+
+def test_date_steps_same_with_and_without_emulation():
+    """The n x n x P products of the date step on the INT8 path and on the DMMA path agree far inside 1e-8."""
+    from conftest import relerr
+    from pfml_b200 import _lib, device, synthetic
+    lib = _lib.load()
+    panel = synthetic.make_panel(N=150, T=15, p=64, seed=31, ragged=0.03)
+    months = [12, 13, 14]
+    try:
+        lib.pfml_set_emulation(1)
+        a = device.date_steps(panel, months)
+        lib.pfml_set_emulation(0)
+        b = device.date_steps(panel, months)
+    finally:
+        lib.pfml_set_emulation(1)
+    for x, y in zip(a, b):
+        assert x["status"] == 0 and y["status"] == 0
+        for key in ("r_tilde", "denom", "risk", "tc", "signal_t"):
+            assert relerr(x[key], y[key]) < 1e-10, key
