@@ -139,11 +139,15 @@ __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t da, uint64_t d
   asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n"
                ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ bool elect_one() {      // one lane of a converged warp; lets ptxas issue the tensor ops without a per-lane loop
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\telect.sync rx|px, %1;\n\t@px mov.s32 %0, 1;\n\t}\n" : "+r"(pred) : "r"(0xFFFFFFFFu));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
-constexpr double kLoScale = 1.0 / (double)(1ull << (7 * (ES - 1) - 21));
 
 struct EmuP {
   const int8_t* As; const int8_t* Bs; const double* sa; const double* sb;   // slices and 2^e scales (sb includes 2^-14)
@@ -152,10 +156,14 @@ struct EmuP {
   const double* rs; long s_rs;
   double alpha, beta;
   int M, N, K, MB, NB, batch;
+  int q;                                   // fixed-point position of the recombined sum (see the epilogue)
   int* err;
 };
 
-__global__ void __launch_bounds__(256, 1) emu_gemm_kernel(const EmuP p) {
+constexpr int EPI_G = 4;                                      // column groups of the epilogue -> 4 * EPI_G epilogue warps
+constexpr int EMU_THREADS = 128 + 128 * EPI_G;
+
+__global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + ESTAGES * EA_STAGE;
@@ -170,7 +178,7 @@ __global__ void __launch_bounds__(256, 1) emu_gemm_kernel(const EmuP p) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&empty_bar[s])));
     }
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&acc_full)));
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 128;" ::"r"(smem_u32(&acc_empty)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&acc_empty)), "r"(128 * EPI_G));
     asm volatile("fence.mbarrier_init.release.cluster;");
   }
   if (warp == 2) {
@@ -182,7 +190,7 @@ __global__ void __launch_bounds__(256, 1) emu_gemm_kernel(const EmuP p) {
   asm volatile("tcgen05.fence::after_thread_sync;");
   const uint32_t tbase = tmem_base;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {
     // ===== producer: one bulk copy per operand per stage; runs ahead into the next tile while the epilogue works =====
     long it = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
@@ -192,15 +200,18 @@ __global__ void __launch_bounds__(256, 1) emu_gemm_kernel(const EmuP p) {
       for (int kc = 0; kc < KB; kc++, it++) {
         const int s = (int)(it % ESTAGES);
         if (!mbar_wait(smem_u32(&empty_bar[s]), (uint32_t)(((it / ESTAGES) & 1) ^ 1))) { atomicOr(p.err, 1); return; }
-        const uint32_t fb = smem_u32(&full_bar[s]);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(EA_STAGE + EB_STAGE) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     ::"r"(smem_u32(sA + s * EA_STAGE)), "l"(a_src + (long)kc * EA_STAGE), "r"(EA_STAGE), "r"(fb) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     ::"r"(smem_u32(sB + s * EB_STAGE)), "l"(b_src + (long)kc * EB_STAGE), "r"(EB_STAGE), "r"(fb) : "memory");
+        if (elect_one()) {
+          const uint32_t fb = smem_u32(&full_bar[s]);
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(EA_STAGE + EB_STAGE) : "memory");
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"(smem_u32(sA + s * EA_STAGE)), "l"(a_src + (long)kc * EA_STAGE), "r"(EA_STAGE), "r"(fb) : "memory");
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"(smem_u32(sB + s * EB_STAGE)), "l"(b_src + (long)kc * EB_STAGE), "r"(EB_STAGE), "r"(fb) : "memory");
+        }
+        __syncwarp();
       }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1) {
     // ===== MMA issuer: 36 slice pairs x 2 k-steps per stage, accumulator d = i + j at TMEM column d * 64 =====
     const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(EBN >> 3) << 17) | ((uint32_t)(EBM >> 4) << 24);
     long it = 0;
@@ -213,6 +224,7 @@ __global__ void __launch_bounds__(256, 1) emu_gemm_kernel(const EmuP p) {
         if (!mbar_wait(smem_u32(&full_bar[s]), (uint32_t)((it / ESTAGES) & 1))) { atomicOr(p.err, 2); return; }
         asm volatile("tcgen05.fence::after_thread_sync;");
         const uint64_t da0 = make_desc(smem_u32(sA + s * EA_STAGE)), db0 = make_desc(smem_u32(sB + s * EB_STAGE));
+        if (elect_one()) {
         if (kc == 0) {
 #pragma unroll
           for (int i = 0; i < ES; i++)
@@ -233,57 +245,76 @@ __global__ void __launch_bounds__(256, 1) emu_gemm_kernel(const EmuP p) {
                         db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, 1u);
         }
         umma_commit(smem_u32(&empty_bar[s]));
+        }
+        __syncwarp();
       }
-      umma_commit(smem_u32(&acc_full));
+      if (elect_one()) umma_commit(smem_u32(&acc_full));
+      __syncwarp();
     }
   } else if (warp >= 4) {
-    // ===== epilogue =====
-    const int q = warp & 3;
+    // ===== epilogue: EPI_WARPS warps, warp = (lane quarter q of TMEM, column group g of EBN / EPI_G columns) =====
+    // Many warps because this part is latency-bound (about 35 dependent integer / FP64 instructions per element): with one
+    // warp per scheduler it took longer than the products of the tile.
+    const int q = warp & 3, g = (warp - 4) >> 2;
+    constexpr int GC = EBN / EPI_G;                 // columns per warp
+    const int shl = p.q - 21, shr = 7 * (ES - 1) - p.q;
     int tl = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x, tl++) {
       const int nb = (int)(t % p.NB), mb = (int)((t / p.NB) % p.MB), z = (int)(t / ((long)p.NB * p.MB));
-      if (!mbar_wait(smem_u32(&acc_full), (uint32_t)(tl & 1))) { atomicOr(p.err, 8); return; }
-      asm volatile("tcgen05.fence::after_thread_sync;");
       const int row = mb * EBM + q * 32 + lane;
       const bool rok = row < p.M;
-      double rsv = rok ? p.alpha * p.sa[(long)z * p.M + row] : 0.0;
+      // the operand scales are powers of two: they go into the exponent field instead of FP64 multiplies
+      const int ea = rok ? (int)((__double_as_longlong(p.sa[(long)z * p.M + row]) >> 52) & 0x7ff) - 1023 - p.q : 0;
+      double rsv = rok ? p.alpha : 0.0;
       if (p.rs && rok) rsv *= p.rs[(long)z * p.s_rs + row];
-      double* drow = p.D + (long)z * p.sD + (long)row * p.ldd + (long)nb * EBN;
-      const double* erow = p.E ? p.E + (long)z * p.sE + (long)row * p.lde + (long)nb * EBN : nullptr;
-      const double* sbz = p.sb + (long)z * p.N + (long)nb * EBN;
-      for (int c0 = 0; c0 < EBN; c0 += 16) {
-        long long hi[16], lo[16];
+      const int colbase = nb * EBN + g * GC;
+      double* drow = p.D + (long)z * p.sD + (long)row * p.ldd + colbase;
+      const double* erow = p.E ? p.E + (long)z * p.sE + (long)row * p.lde + colbase : nullptr;
+      const double* sbz = p.sb + (long)z * p.N + colbase;
+      if (!mbar_wait(smem_u32(&acc_full), (uint32_t)(tl & 1))) { atomicOr(p.err, 8); return; }
+      asm volatile("tcgen05.fence::after_thread_sync;");
+      // phase 1 (the issuer waits for it): drain this warp's columns from TMEM into fixed-point sums, hand TMEM back
+      long long S[GC];
 #pragma unroll
-        for (int c = 0; c < 16; c++) hi[c] = lo[c] = 0;
-        uint32_t v[ES][16];
+      for (int c0 = 0; c0 < GC; c0 += 8) {
+        uint32_t v[ES][8];
 #pragma unroll
         for (int d = 0; d < ES; d++)
-          asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                       : "=r"(v[d][0]), "=r"(v[d][1]), "=r"(v[d][2]), "=r"(v[d][3]), "=r"(v[d][4]), "=r"(v[d][5]), "=r"(v[d][6]), "=r"(v[d][7]),
-                         "=r"(v[d][8]), "=r"(v[d][9]), "=r"(v[d][10]), "=r"(v[d][11]), "=r"(v[d][12]), "=r"(v[d][13]), "=r"(v[d][14]), "=r"(v[d][15])
-                       : "r"(tbase + ((uint32_t)(q * 32) << 16) + d * EBN + c0));
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                       : "=r"(v[d][0]), "=r"(v[d][1]), "=r"(v[d][2]), "=r"(v[d][3]), "=r"(v[d][4]), "=r"(v[d][5]), "=r"(v[d][6]), "=r"(v[d][7])
+                       : "r"(tbase + ((uint32_t)(q * 32) << 16) + d * EBN + g * GC + c0));
         asm volatile("tcgen05.wait::ld.sync.aligned;");
-        if (c0 + 16 >= EBN) {                    // last chunk read: hand TMEM back to the MMA issuer before the stores
+        if (c0 + 8 >= GC) {
           asm volatile("tcgen05.fence::before_thread_sync;");
           asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&acc_empty)) : "memory");
         }
 #pragma unroll
-        for (int d = 0; d < ES; d++)
+        for (int c = 0; c < 8; c++) {
+          long long hi = 0, lo = 0;
 #pragma unroll
-          for (int c = 0; c < 16; c++) {
-            if (d < 4) hi[c] = hi[c] * 128 + (long long)(int32_t)v[d][c];
-            else lo[c] = lo[c] * 128 + (long long)(int32_t)v[d][c];
+          for (int d = 0; d < ES; d++) {
+            if (d < 4) hi = hi * 128 + (long long)(int32_t)v[d][c];
+            else lo = lo * 128 + (long long)(int32_t)v[d][c];
           }
-        if (rok) {
+          // S = V 2^q with V = sum_d acc_d 2^(-7 d): the bits of the low slices below 2^-q are dropped (q is chosen from K
+          // so that S fits 63 bits; the dropped part is < 2^(-q-14) of max|a| max|b|, below the slicing error)
+          S[c0 + c] = (hi << shl) + (lo >> shr);
+        }
+      }
+      // phase 2 (overlaps the next tile's products): scale and store
+      if (rok) {
 #pragma unroll
-          for (int c = 0; c < 16; c++) {
-            const int col = nb * EBN + c0 + c;
-            if (col < p.N) {
-              const double x = ((double)hi[c] + (double)lo[c] * kLoScale) * 4.76837158203125e-07;   // 2^-(7 (ES-1) - 21), 2^-21
-              double o = rsv * (x * sbz[c0 + c]);
-              if (erow) o += p.beta * erow[c0 + c];
-              drow[c0 + c] = o;
-            }
+        for (int c = 0; c < GC; c++) {
+          if (colbase + c < p.N) {
+            const double x0 = (double)S[c];
+            const int e = ea + (int)((__double_as_longlong(sbz[c]) >> 52) & 0x7ff) - 1023;
+            const int h0 = __double2hiint(x0), nf = ((h0 >> 20) & 0x7ff) + e;
+            // exponent out of range: flush to zero / overflow to infinity (never seen with the panel's magnitudes)
+            const int h1 = (S[c] == 0 || nf <= 0) ? 0 : (nf >= 2047 ? ((h0 & 0x80000000) | 0x7ff00000) : h0 + (e << 20));
+            const int l1 = (S[c] == 0 || nf <= 0 || nf >= 2047) ? 0 : __double2loint(x0);
+            double o = rsv * __hiloint2double(h1, l1);
+            if (erow) o += p.beta * erow[c];
+            drow[c] = o;
           }
         }
       }
@@ -332,6 +363,7 @@ int emu_mma(const int8_t* As, const double* sa, const int8_t* Bs, const double* 
   p.As = As; p.Bs = Bs; p.sa = sa; p.sb = sb; p.D = D; p.ldd = ldd; p.sD = sD; p.E = E; p.lde = lde; p.sE = sE;
   p.rs = rs; p.s_rs = s_rs; p.alpha = alpha; p.beta = beta; p.M = M; p.N = N; p.K = K;
   p.MB = ceil_div(M, EBM); p.NB = ceil_div(N, EBN); p.batch = batch; p.err = err;
+  p.q = K <= 512 ? 38 : 33;               // |V| < 1.02 K 127^2: 2^23.1 (K <= 512), 2^28.1 (K <= 16640)
   constexpr size_t smem = (size_t)ESTAGES * (EA_STAGE + EB_STAGE);
   static bool cfg[64] = {};
   static int n_sm[64] = {};
@@ -347,7 +379,7 @@ int emu_mma(const int8_t* As, const double* sa, const int8_t* Bs, const double* 
   const long want = mult > 0 ? (long)mult * n_sm[dev & 63] : tiles;
   const int grid = (int)(tiles < want ? tiles : want);
   prof_begin(-2, s);
-  emu_gemm_kernel<<<grid, 256, smem, s>>>(p);
+  emu_gemm_kernel<<<grid, EMU_THREADS, smem, s>>>(p);
   PFML_CHECK_LAUNCH();
   prof_end(-2, s, 2.0 * M * (double)N * K * batch, 0.0);
   return 0;
