@@ -75,6 +75,15 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
 int emu_mma(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
             const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD, int* err,
             cudaStream_t s);
+// optional epilogue extras of emu_mma: o = cs[col] * o (+ diag on the diagonal), and a second output D2 = E2 + o
+struct EmuExtra {
+  const double* cs = nullptr; long s_cs = 0;
+  double diag = 0.0;
+  double* D2 = nullptr; const double* E2 = nullptr; long ld2 = 0, s2 = 0;
+};
+int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
+               const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD,
+               const EmuExtra& x, int* err, cudaStream_t s);
 
 // profiling categories (device-time accounting with CUDA events, see prof.cu)
 enum ProfTag { T_OTHER = 0, T_STD = 1, T_MFUNC = 2, T_CHAIN = 3, T_HORNER = 4, T_SOLVE = 5, T_DENOM = 6,

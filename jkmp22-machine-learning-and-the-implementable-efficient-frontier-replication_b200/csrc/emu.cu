@@ -156,6 +156,8 @@ struct EmuP {
   const double* rs; long s_rs;
   double alpha, beta;
   int M, N, K, MB, NB, batch;
+  const double* cs; long s_cs; double diag;
+  double* D2; const double* E2; long ld2, s2;
   int q;                                   // fixed-point position of the recombined sum (see the epilogue)
   int* err;
 };
@@ -256,6 +258,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
     // Many warps because this part is latency-bound (about 35 dependent integer / FP64 instructions per element): with one
     // warp per scheduler it took longer than the products of the tile.
     const int q = warp & 3, g = (warp - 4) >> 2;
+    double* stg = reinterpret_cast<double*>(smem + ESTAGES * (EA_STAGE + EB_STAGE)) + (warp - 4) * (32 * 9);   // 32 x 8 (+1 pad)
     constexpr int GC = EBN / EPI_G;                 // columns per warp
     const int shl = p.q - 21, shr = 7 * (ES - 1) - p.q;
     int tl = 0;
@@ -268,8 +271,6 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
       double rsv = rok ? p.alpha : 0.0;
       if (p.rs && rok) rsv *= p.rs[(long)z * p.s_rs + row];
       const int colbase = nb * EBN + g * GC;
-      double* drow = p.D + (long)z * p.sD + (long)row * p.ldd + colbase;
-      const double* erow = p.E ? p.E + (long)z * p.sE + (long)row * p.lde + colbase : nullptr;
       const double* sbz = p.sb + (long)z * p.N + colbase;
       if (!mbar_wait(smem_u32(&acc_full), (uint32_t)(tl & 1))) { atomicOr(p.err, 8); return; }
       asm volatile("tcgen05.fence::after_thread_sync;");
@@ -301,22 +302,43 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
           S[c0 + c] = (hi << shl) + (lo >> shr);
         }
       }
-      // phase 2 (overlaps the next tile's products): scale and store
-      if (rok) {
+      // phase 2 (overlaps the next tile's products): scale, then store through a per-warp transpose in shared memory so
+      // that one global instruction covers 4 rows x 64 contiguous bytes instead of 32 rows x 8 bytes
+      const int rr = lane >> 3, cc = lane & 7;
 #pragma unroll
-        for (int c = 0; c < GC; c++) {
-          if (colbase + c < p.N) {
-            const double x0 = (double)S[c];
-            const int e = ea + (int)((__double_as_longlong(sbz[c]) >> 52) & 0x7ff) - 1023;
-            const int h0 = __double2hiint(x0), nf = ((h0 >> 20) & 0x7ff) + e;
-            // exponent out of range: flush to zero / overflow to infinity (never seen with the panel's magnitudes)
-            const int h1 = (S[c] == 0 || nf <= 0) ? 0 : (nf >= 2047 ? ((h0 & 0x80000000) | 0x7ff00000) : h0 + (e << 20));
-            const int l1 = (S[c] == 0 || nf <= 0 || nf >= 2047) ? 0 : __double2loint(x0);
-            double o = rsv * __hiloint2double(h1, l1);
-            if (erow) o += p.beta * erow[c];
-            drow[c] = o;
+      for (int c0 = 0; c0 < GC; c0 += 8) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+          const double x0 = (double)S[c0 + c];
+          const int col = colbase + c0 + c;
+          const int e = ea + (col < p.N ? (int)((__double_as_longlong(sbz[c0 + c]) >> 52) & 0x7ff) - 1023 : 0);
+          const int h0 = __double2hiint(x0), nf = ((h0 >> 20) & 0x7ff) + e;
+          // exponent out of range: flush to zero / overflow to infinity (never seen with the panel's magnitudes)
+          const int h1 = (S[c0 + c] == 0 || nf <= 0) ? 0 : (nf >= 2047 ? ((h0 & 0x80000000) | 0x7ff00000) : h0 + (e << 20));
+          const int l1 = (S[c0 + c] == 0 || nf <= 0 || nf >= 2047) ? 0 : __double2loint(x0);
+          stg[lane * 9 + c] = rsv * __hiloint2double(h1, l1);
+        }
+        __syncwarp();
+        const int col = colbase + c0 + cc;
+        if (col < p.N) {
+          const double csv = p.cs ? p.cs[(long)z * p.s_cs + col] : 1.0;
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const int r = mb * EBM + q * 32 + i * 4 + rr;
+            if (r < p.M) {
+              double o = stg[(i * 4 + rr) * 9 + cc];
+              if (p.E) o += p.beta * p.E[(long)z * p.sE + (long)r * p.lde + col];
+              o *= csv;
+              if (r == col) o += p.diag;
+              p.D[(long)z * p.sD + (long)r * p.ldd + col] = o;
+              if (p.D2) {
+                const long o2 = (long)z * p.s2 + (long)r * p.ld2 + col;
+                p.D2[o2] = p.E2[o2] + o;
+              }
+            }
           }
         }
+        __syncwarp();
       }
     }
   }
@@ -355,6 +377,12 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
 int emu_mma(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
             const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD, int* err,
             cudaStream_t s) {
+  return emu_mma_ex(As, sa, Bs, sb, M, N, K, batch, alpha, rs, s_rs, beta, E, lde, sE, D, ldd, sD, EmuExtra(), err, s);
+}
+
+int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
+               const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD,
+               const EmuExtra& x, int* err, cudaStream_t s) {
   if (!emu_shape_ok(M, N, K)) {
     set_error("emu_mma: unsupported shape M=%d N=%d K=%d", M, N, K);
     return -2;
@@ -363,8 +391,9 @@ int emu_mma(const int8_t* As, const double* sa, const int8_t* Bs, const double* 
   p.As = As; p.Bs = Bs; p.sa = sa; p.sb = sb; p.D = D; p.ldd = ldd; p.sD = sD; p.E = E; p.lde = lde; p.sE = sE;
   p.rs = rs; p.s_rs = s_rs; p.alpha = alpha; p.beta = beta; p.M = M; p.N = N; p.K = K;
   p.MB = ceil_div(M, EBM); p.NB = ceil_div(N, EBN); p.batch = batch; p.err = err;
+  p.cs = x.cs; p.s_cs = x.s_cs; p.diag = x.diag; p.D2 = x.D2; p.E2 = x.E2; p.ld2 = x.ld2; p.s2 = x.s2;
   p.q = K <= 512 ? 38 : 33;               // |V| < 1.02 K 127^2: 2^23.1 (K <= 512), 2^28.1 (K <= 16640)
-  constexpr size_t smem = (size_t)ESTAGES * (EA_STAGE + EB_STAGE);
+  constexpr size_t smem = (size_t)ESTAGES * (EA_STAGE + EB_STAGE) + (size_t)(4 * EPI_G) * 32 * 9 * sizeof(double);
   static bool cfg[64] = {};
   static int n_sm[64] = {};
   int dev = 0;

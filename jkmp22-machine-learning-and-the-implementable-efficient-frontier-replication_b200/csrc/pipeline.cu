@@ -299,9 +299,10 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.BS = c.take<double>((size_t)B * (NP + KP) * w.ldP);
   w.OMC = c.take<double>(BnP);
   w.eAs = c.take<int8_t>(emu_a_slices_bytes(B, NP, NP));
-  w.eBs = c.take<int8_t>(emu_b_slices_bytes(B, NP, P));
-  w.esa = c.take<double>((size_t)B * NP); w.esb = c.take<double>((size_t)B * P);
-  w.eex = c.take<int>((size_t)B * P); w.eerr = c.take<int>(64);
+  const int Pn = P > NP ? P : NP;          // B operands are n x P (Horner, solves) or n x n (chain)
+  w.eBs = c.take<int8_t>(emu_b_slices_bytes(B, NP, Pn));
+  w.esa = c.take<double>((size_t)B * NP); w.esb = c.take<double>((size_t)B * Pn);
+  w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64);
   w.risk_tmp = need_risk ? c.take<double>((size_t)B * P * P) : nullptr;
   w.tc_tmp = need_tc ? c.take<double>((size_t)B * P * P) : nullptr;
   w.bytes = c.off;
@@ -371,39 +372,66 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
   double* spare = (mt == w.m.mt) ? w.m.Xinv : w.m.mt;
 
+  const bool emu = use_emu() && emu_shape_ok(NP, P, NP);
+  const bool emu_nn = emu && emu_shape_ok(NP, NP, NP);
+  const double* emu_a_cur = nullptr;       // whose slices currently sit in w.eAs
+  if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int), s));
+
   // ---- a7 chain of n x n products (tilde domain) ------------------------------------------------
   //   B~_1 = m~ G_1, B~_{k+1} = B~_k m~ G_{k+1};  CB = sum_{k=0}^{lb-1} B~_k;  B11 = B~_lb
   {
     ProfScope ps(T_CHAIN, s);
     PFML_TRY(chain_init(B, NP, mt, gv(1), sg, Bt_a, CB, s));
-    GemmP g;
-    g.lda = g.ldb = g.ldd = NP; g.sA = g.sB = g.sD = NN;
-    g.M = g.N = g.K = NP;
-    for (int k = 1; k < lb; k++) {
-      const bool last = (k == lb - 1);
-      g.A = Bt_a; g.B = mt; g.D = last ? B11 : Bt_b;
-      g.cs = gv(k + 1); g.s_cs = sg;
-      g.D2 = last ? nullptr : CB; g.E2 = last ? nullptr : CB;
-      PFML_TRY(gemm(g, B, s));
-      double* t = Bt_a; Bt_a = Bt_b; Bt_b = t;
+    if (emu_nn) {
+      // INT8 tensor-core path: m~ is the B operand of every product (sliced once), B~_k the A operand
+      PFML_TRY(emu_slice_b(mt, NP, NN, NP, NP, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      for (int k = 1; k < lb; k++) {
+        const bool last = (k == lb - 1);
+        PFML_TRY(emu_slice_a(Bt_a, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+        EmuExtra x;
+        x.cs = gv(k + 1); x.s_cs = sg;
+        if (!last) { x.D2 = CB; x.E2 = CB; x.ld2 = NP; x.s2 = NN; }
+        PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, NP, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, last ? B11 : Bt_b, NP, NN, x,
+                            w.eerr, s));
+        double* t = Bt_a; Bt_a = Bt_b; Bt_b = t;
+      }
+    } else {
+      GemmP g;
+      g.lda = g.ldb = g.ldd = NP; g.sA = g.sB = g.sD = NN;
+      g.M = g.N = g.K = NP;
+      for (int k = 1; k < lb; k++) {
+        const bool last = (k == lb - 1);
+        g.A = Bt_a; g.B = mt; g.D = last ? B11 : Bt_b;
+        g.cs = gv(k + 1); g.s_cs = sg;
+        g.D2 = last ? nullptr : CB; g.E2 = last ? nullptr : CB;
+        PFML_TRY(gemm(g, B, s));
+        double* t = Bt_a; Bt_a = Bt_b; Bt_b = t;
+      }
     }
     // const_l1~ = CB + B11 -> Wk (to be inverted);  const~ = I + m~ (G_0 CB) -> spare (to be inverted)
     PFML_TRY(add_mat(B, NN, CB, B11, w.m.Wk, s));
     PFML_TRY(row_scale(B, NP, NP, NP, NN, CB, gv(0), sg, CBs, NP, NN, s));
-    GemmP c;
-    c.lda = c.ldb = c.ldd = NP; c.sA = c.sB = c.sD = NN;
-    c.M = c.N = c.K = NP;
-    c.A = mt; c.B = CBs; c.D = spare; c.diag = 1.0;
-    PFML_TRY(gemm(c, B, s));
+    if (emu_nn) {
+      PFML_TRY(emu_slice_a(mt, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+      emu_a_cur = mt;                    // the Horner products below reuse these slices of m~
+      PFML_TRY(emu_slice_b(CBs, NP, NN, NP, NP, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      EmuExtra x;
+      x.diag = 1.0;
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, NP, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, spare, NP, NN, x, w.eerr, s));
+    } else {
+      GemmP c;
+      c.lda = c.ldb = c.ldd = NP; c.sA = c.sB = c.sD = NN;
+      c.M = c.N = c.K = NP;
+      c.A = mt; c.B = CBs; c.D = spare; c.diag = 1.0;
+      PFML_TRY(gemm(c, B, s));
+    }
   }
 
   // ---- a8 Horner accumulation of the n x P sums -------------------------------------------------
   //   Z'_j = G_j (S~_{j+1} + m~ Z'_{j+1}),  Z'_{lb-1} = G_{lb-1} S~_lb ;  Z = S~_1 + m~ Z'_1
   //   N = S~_0 + m~ G_0 Z ;  N_l1 = Z + B11 S~_{lb+1}
   double* Z = nullptr;
-  const bool emu = use_emu() && emu_shape_ok(NP, P, NP);
   // one n x n x P product D = alpha * rs o (A X) + E on whichever tensor pipe is selected; A is sliced on demand
-  const double* emu_a_cur = nullptr;
   auto nxP = [&](const double* A, const double* X, long sX, double alpha, const double* rs, long s_rs, const double* E, long sE,
                  double* D, long sD) -> int {
     if (emu) {
@@ -420,7 +448,6 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     if (E) { g.E = E; g.lde = ldP; g.sE = sE; g.beta = 1.0; }
     return gemm(g, B, s);
   };
-  if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int), s));
   {
     ProfScope ps(T_HORNER, s);
     const double* Zp = St(lb);         // already scaled by g_{lb-1} in the standardise kernel
