@@ -9,7 +9,8 @@ so ranks shard them with no data-path collective (weak scaling: every rank runs 
 
 Printed JSON line (rank 0): value = whole-job date-steps/s with inputs resident in HBM; e2e = the same through
 pfml_date_steps_host (pinned HOST buffers in, HOST buffers out, H2D/D2H inside the timed region); roofline = the
-dominant kernel (the batched FP64 DMMA GEMM) against the FP64 GEMM peak measured in this run; cpu_baseline = the
+dominant kernel (the FP64-equivalent batched GEMM on the INT8 tensor cores) against the tensor-pipe ceiling derived
+from MEASURED_PEAKS.json, with the cuBLAS DGEMM peak measured in this run beside it; cpu_baseline = the
 numpy oracle (a port of the reference's algorithm) on the host cores.  --impl reference times only that CPU arm.
 """
 from __future__ import annotations
@@ -336,22 +337,36 @@ def run_ours(args, rank, world, local_rank):
     if rank != 0:
         return
     # ---- roofline of the dominant kernel ---------------------------------------------------------------
-    # The dominant launch is the Horner step m~ [n x n] @ Z [n x P] for the whole batch (12 launches per step, all
-    # the same shape; SURVEY 8d counts them as 24 n^2 P flops per date = 2 n^2 P per launch and date).  Its duration
-    # is the `horner_nxP` stage (CUDA events around those 12 launches plus one row-scaling kernel, < 1%) / 12.
-    peak = measure_fp64_peak(torch, dev)
+    # The dominant kernel is pfml::emu_gemm_kernel: the n x n x P products of the Horner / solve steps (14 launches per
+    # step) and the n x n x n chain products (11 launches) as FP64-equivalent GEMMs on the INT8 tensor cores.  Its
+    # duration is measured live with CUDA events around every launch (library profiling slot `emu_i8_gemm`), the
+    # algorithmic work is 2 M N K FP64 flops per product.  One FP64-equivalent product costs 28 int8 slice products,
+    # so the tensor-pipe ceiling in FP64-equivalent flops is (INT8 dense peak) / 28; the INT8 dense peak is taken as
+    # 2 x the measured bf16 GEMM peak of MEASURED_PEAKS.json (sustained figure: the kernel is timed inside a long step).
+    peak_fp64 = measure_fp64_peak(torch, dev)
     off = official_flops_per_date()
+    k_emu = names.index("emu_i8_gemm")
+    emu_ms = pms[k_emu] / args.steps
+    emu_launches = pln[k_emu] / args.steps
+    emu_flops = pfl[k_emu] / args.steps
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        bf16_peak = float(json.load(open(peaks_path)).get("bf16_tflops_sustained", 1400.0))
+        peak_src = "2 x bf16_tflops_sustained of MEASURED_PEAKS.json (%.1f) / 28 slice products, of measured" % bf16_peak
+    else:
+        bf16_peak = 1400.0
+        peak_src = "2 x 1400 TFLOP/s (sustained bf16 fallback of B200_PROFILING.md) / 28 slice products, of fallback"
+    n_pairs = 28
+    peak = 2.0 * bf16_peak / n_pairs
+    achieved = emu_flops / (emu_ms * 1e-3) * 1e-12 if emu_ms > 0 else 0.0
     horner_ms = pms[4] / args.steps
-    launch_ms = horner_ms / 12.0
-    flops_per_launch = 2.0 * N_STOCKS * N_STOCKS * (P_FEAT + 1) * B
-    achieved = flops_per_launch / (launch_ms * 1e-3) * 1e-12
     gemm_ms = pms[0] / args.steps                      # all DMMA GEMM launches of one step
     total_stage_ms = sum(pms[1:7]) / args.steps
     traffic = None
     ncu_json = os.path.join(ROOT, "profiles", "ncu_summary.json")
     if os.path.exists(ncu_json):
         try:
-            per_date = json.load(open(ncu_json)).get("horner_gemm_dram_bytes_per_launch_per_date")
+            per_date = json.load(open(ncu_json)).get("emu_gemm_nxP_dram_bytes_per_launch_per_date")
             traffic = per_date * B if per_date else None
         except Exception:
             traffic = None
@@ -377,17 +392,22 @@ def run_ours(args, rank, world, local_rank):
                 "outputs": "r_tilde, denom, risk, tc, signal_t (everything PFML_Input_Data.py stores per date)",
                 "chunk": args.chunk, "max_abs_diff_vs_resident_path": chk},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "pfml::gemm_kernel<64,64,32,32,16,3,3> on the Horner step (batch x [512 x 1025 x 512], FP64 DMMA)",
+        "roofline": {"bound": "tensor",
+                     "kernel": "pfml::emu_gemm_kernel (tcgen05.mma kind::i8, TMEM accumulators, bulk-TMA operands): FP64-equivalent "
+                               "batched products [512 x 1025 x 512] (Horner, solves) and [512 x 512 x 512] (chain)",
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
-                     "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, best of 5, measured in this run "
-                                    "(MEASURED_PEAKS.json has no FP64 figure; DMMA issue peak 37.05 TFLOP/s, profiles/r01_fp64_peak_microbench.log)",
-                     "algorithmic_flops_per_launch": flops_per_launch, "launch_ms": launch_ms, "launches_per_step": 12,
-                     "share_of_step": horner_ms / (ms_total / args.steps),
-                     "all_gemm_launches": {"algorithmic_tflops": off["total"] * B / (gemm_ms * 1e-3) * 1e-12,
-                                           "executed_tflops": pfl[0] / args.steps / (gemm_ms * 1e-3) * 1e-12,
-                                           "ms_per_step": gemm_ms, "launches_per_step": pln[0] / args.steps,
-                                           "share_of_step": gemm_ms / (ms_total / args.steps),
-                                           "algorithmic_flops_per_date": off["total"]}},
+                     "traffic_note": "DRAM bytes of one n x P launch (ncu --set full, profiles/ncu_summary.json)",
+                     "flop_kind": "FP64-equivalent (algorithmic 2 M N K per product); executed INT8 rate = 28 x achieved x padding",
+                     "peak_source": peak_src,
+                     "executed_int8_tops": achieved * n_pairs * (1088.0 / 1025.0),
+                     "vs_cublas_dgemm_peak": achieved / peak_fp64, "cublas_dgemm_peak_tflops": peak_fp64,
+                     "algorithmic_flops_per_step": emu_flops, "launch_ms_avg": emu_ms / max(emu_launches, 1.0),
+                     "launches_per_step": emu_launches, "share_of_step": emu_ms / (ms_total / args.steps),
+                     "dmma_gemm_launches": {"executed_tflops": pfl[0] / args.steps / (gemm_ms * 1e-3) * 1e-12,
+                                            "ms_per_step": gemm_ms, "launches_per_step": pln[0] / args.steps,
+                                            "share_of_step": gemm_ms / (ms_total / args.steps),
+                                            "peak": peak_fp64, "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, best of 5, this run"},
+                     "algorithmic_flops_per_date": off["total"]},
         "hp_grid": hp,
         "stages": stages,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",

@@ -89,6 +89,40 @@ __global__ void slice_kmajor_kernel(const double* __restrict__ X, long ld, long 
   }
 }
 
+// The same for K == 512 in one pass over the data: a warp per row, every lane keeps its 16 consecutive values in
+// registers between the row maximum and the slicing.
+template <int BR>
+__global__ void __launch_bounds__(256)
+slice_kmajor512_kernel(const double* __restrict__ X, long ld, long sX, int R, int8_t* __restrict__ out,
+                       double* __restrict__ scale, double extra, int* __restrict__ err) {
+  constexpr int K = 512, KB = K / EKC;
+  const int z = blockIdx.y, row = blockIdx.x * 8 + threadIdx.x / 32, lane = threadIdx.x & 31;
+  const int RB = (R + BR - 1) / BR;
+  if (row >= RB * BR) return;
+  constexpr long STAGE = (long)ES * BR * EKC;
+  int8_t* base = out + (((long)z * RB + row / BR) * KB) * STAGE;
+  double x[16];
+  int e = 0;
+  if (row < R) {
+    const double2* a = reinterpret_cast<const double2*>(X + (long)z * sX + (long)row * ld + lane * 16);
+    double mx = 0.0;
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { const double2 v = a[k]; x[2 * k] = v.x; x[2 * k + 1] = v.y; }
+#pragma unroll
+    for (int k = 0; k < 16; k++) { const double v = fabs(x[k]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (bad) atomicOr(err, 16);
+    e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
+    if (lane == 0) scale[(long)z * R + row] = scalbn(extra, e);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 16; k++) x[k] = 0.0;
+  }
+  const int k0 = lane * 16;
+  slice16(x, e, base + (long)(k0 / EKC) * STAGE + canon(row % BR, k0 % EKC), (long)BR * EKC);
+}
+
 // B-type operand: X [K][C] with C contiguous (ld), scaled per column, blocks of 64 columns.
 __global__ void col_exponent_kernel(const double* __restrict__ X, long ld, long sX, int K, int C, int* __restrict__ ex,
                                     double* __restrict__ scale, double extra, int* __restrict__ err) {
@@ -116,6 +150,49 @@ slice_nmajor_kernel(const double* __restrict__ X, long ld, long sX, int K, int C
 #pragma unroll
   for (int k = 0; k < 16; k++) x[k] = n < C ? X[(long)z * sX + (long)(k0 + k) * ld + n] : 0.0;
   slice16(x, e, base + canon(nn, kq * 16), (long)EBN * EKC);
+}
+
+// B-type operand with K == 512 in one pass: a CTA owns 32 columns x all 512 k (thread = column, 32 consecutive k held
+// in registers), the column maxima go through shared memory, no separate exponent kernel.
+__global__ void __launch_bounds__(512, 1)
+slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, int CB, int* __restrict__ ex, double* __restrict__ scale,
+                       double extra, int8_t* __restrict__ out, int* __restrict__ err) {
+  constexpr int K = 512, KB = K / EKC;
+  __shared__ double red[16][33];
+  const int z = blockIdx.y, lane = threadIdx.x & 31, kq = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + lane, cb = n / EBN, nn = n % EBN;
+  double x[32];
+  double mx = 0.0;
+  bool bad = false;
+  if (n < C) {
+    const double* b = X + (long)z * sX + (long)(kq * 32) * ld + n;
+#pragma unroll
+    for (int j = 0; j < 32; j++) x[j] = b[(long)j * ld];
+#pragma unroll
+    for (int j = 0; j < 32; j++) { const double v = fabs(x[j]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; j++) x[j] = 0.0;
+  }
+  if (bad) atomicOr(err, 16);
+  red[kq][lane] = mx;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 16; j++) mx = fmax(mx, red[j][lane]);
+  const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
+  if (kq == 0 && n < C) {
+    ex[(long)z * C + n] = e;
+    scale[(long)z * C + n] = scalbn(extra, e);
+  }
+  if (cb >= CB) return;
+  int8_t* base = out + (((long)z * CB + cb) * KB + kq / 2) * (long)EB_STAGE;
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    double y[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) y[j] = x[h * 16 + j];
+    slice16(y, e, base + canon(nn, (kq & 1) * 32 + h * 16), (long)EBN * EKC);
+  }
 }
 
 }  // namespace
@@ -358,7 +435,10 @@ bool emu_shape_ok(int M, int N, int K) { return M > 0 && N > 0 && K >= EKC && K 
 // A [M][K] (K contiguous) -> slices + row scales 2^ea
 int emu_slice_a(const double* A, long lda, long sA, int M, int K, int batch, int8_t* out, double* scale, int* err, cudaStream_t s) {
   const int rows = ceil_div(M, EBM) * EBM;
-  slice_kmajor_kernel<EBM><<<dim3(ceil_div(rows, 8), batch), 256, 0, s>>>(A, lda, sA, M, K, out, scale, 1.0, err);
+  if (K == 512 && (lda % 2) == 0 && (sA % 2) == 0 && ((uintptr_t)A % 16) == 0)
+    slice_kmajor512_kernel<EBM><<<dim3(ceil_div(rows, 8), batch), 256, 0, s>>>(A, lda, sA, M, out, scale, 1.0, err);
+  else
+    slice_kmajor_kernel<EBM><<<dim3(ceil_div(rows, 8), batch), 256, 0, s>>>(A, lda, sA, M, K, out, scale, 1.0, err);
   PFML_CHECK_LAUNCH();
   return 0;
 }
@@ -366,6 +446,13 @@ int emu_slice_a(const double* A, long lda, long sA, int M, int K, int batch, int
 // B [K][N] (N contiguous) -> slices + column scales 2^(eb - 14); ex [batch][N] is int scratch
 int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int8_t* out, double* scale, int* ex, int* err,
                 cudaStream_t s) {
+  if (K == 512) {
+    // 64-column blocks are written by two CTAs of 32 columns; the padded half of the last block must be zero-filled too
+    slice_nmajor512_kernel<<<dim3(2 * ceil_div(N, EBN), batch), 512, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, 6.103515625e-05,
+                                                                             out, err);
+    PFML_CHECK_LAUNCH();
+    return 0;
+  }
   col_exponent_kernel<<<dim3(ceil_div(N, 128), batch), 128, 0, s>>>(B, ldb, sB, K, N, ex, scale, 6.103515625e-05, err);
   PFML_CHECK_LAUNCH();
   slice_nmajor_kernel<<<dim3(ceil_div(N, EBN), K / EKC, batch), 256, 0, s>>>(B, ldb, sB, K, N, ceil_div(N, EBN), ex, out);

@@ -217,6 +217,20 @@ __global__ void add_kernel(long n, const double* __restrict__ a, const double* _
   for (; i < n; i += stride) out[i] = a[i] + b[i];
 }
 
+// const_l1~ = I + sum_{k=1}^{nk} B~_k + B~_lb  and  G_0 (I + sum_{k=1}^{nk} B~_k) from the stored chain matrices
+struct ChainPtrs { const double* bk[16]; };
+__global__ void chain_sum_kernel(int NP, int nk, ChainPtrs p, const double* __restrict__ b11, const double* __restrict__ g0, long sg,
+                                 double* __restrict__ wk, double* __restrict__ cbs) {
+  const int b = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= NP) return;
+  const long o = ((long)b * NP + r) * NP + c;
+  double acc = (r == c) ? 1.0 : 0.0;
+  for (int k = 0; k < nk; k++) acc += p.bk[k][o];
+  wk[o] = acc + b11[o];
+  cbs[o] = acc * g0[(long)b * sg + r];
+}
+
 // partial Frobenius sums of M, Mi and M - I over a chunk of rows; deterministic two-stage reduction
 __global__ void db_norms_partial_kernel(int NP, const double* __restrict__ M, const double* __restrict__ Mi, double* __restrict__ part) {
   const int b = blockIdx.y, ch = blockIdx.x;
@@ -576,6 +590,16 @@ int copy2(int B, long n_elem, const double* src, double* d1, double* d2, cudaStr
   long n = (long)B * n_elem;
   int blocks = (int)((n + 255) / 256 > 148 * 16 ? 148 * 16 : (n + 255) / 256);
   copy2_kernel<<<blocks, 256, 0, s>>>(n, src, d1, d2);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11, const double* g0, long sg, double* wk, double* cbs,
+              cudaStream_t s) {
+  if (nk > 16) return -1;
+  ChainPtrs p{};
+  for (int k = 0; k < nk; k++) p.bk[k] = bk[k];
+  chain_sum_kernel<<<grid_rc(NP, NP, B), 128, 0, s>>>(NP, nk, p, b11, g0, sg, wk, cbs);
   PFML_CHECK_LAUNCH();
   return 0;
 }

@@ -258,6 +258,7 @@ struct StepWs {
   MtBufs m;
   double *XC, *XCl1, *Ut, *Ev, *G;
   int8_t *eAs, *eBs; double *esa, *esb; int *eex, *eerr;   // INT8-emulated GEMM operands (emu.cu)
+  double* chain;                                            // B~_2 .. B~_{lb-1} of the chain (B~_1 sits in Ya)
   double *St, *Za, *Zb, *Nn, *Nl1, *OM, *BS, *OMC;
   double *risk_tmp, *tc_tmp;
   size_t bytes;
@@ -303,6 +304,7 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.eBs = c.take<int8_t>(emu_b_slices_bytes(B, NP, Pn));
   w.esa = c.take<double>((size_t)B * NP); w.esb = c.take<double>((size_t)B * Pn);
   w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64);
+  w.chain = nt >= 5 ? c.take<double>((size_t)(nt - 4) * BNN) : nullptr;   // lb - 2 matrices
   w.risk_tmp = need_risk ? c.take<double>((size_t)B * P * P) : nullptr;
   w.tc_tmp = need_tc ? c.take<double>((size_t)B * P * P) : nullptr;
   w.bytes = c.off;
@@ -382,19 +384,26 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   {
     ProfScope ps(T_CHAIN, s);
     PFML_TRY(chain_init(B, NP, mt, gv(1), sg, Bt_a, CB, s));
+    const bool keep_all = emu_nn && lb - 1 <= 16 && w.chain != nullptr;
     if (emu_nn) {
-      // INT8 tensor-core path: m~ is the B operand of every product (sliced once), B~_k the A operand
+      // INT8 tensor-core path: m~ is the B operand of every product (sliced once), B~_k the A operand.  Every B~_k is
+      // kept (w.chain) and the sums CB + B11 and G_0 CB are formed by one kernel at the end instead of a read-modify-
+      // write of CB in every epilogue.
       PFML_TRY(emu_slice_b(mt, NP, NN, NP, NP, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      const double* bk[16];
+      bk[0] = Bt_a;
       for (int k = 1; k < lb; k++) {
         const bool last = (k == lb - 1);
         PFML_TRY(emu_slice_a(Bt_a, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
         EmuExtra x;
         x.cs = gv(k + 1); x.s_cs = sg;
-        if (!last) { x.D2 = CB; x.E2 = CB; x.ld2 = NP; x.s2 = NN; }
-        PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, NP, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, last ? B11 : Bt_b, NP, NN, x,
-                            w.eerr, s));
-        double* t = Bt_a; Bt_a = Bt_b; Bt_b = t;
+        double* out = last ? B11 : (keep_all ? w.chain + (size_t)(k - 1) * B * NN : Bt_b);
+        if (!last && !keep_all) { x.D2 = CB; x.E2 = CB; x.ld2 = NP; x.s2 = NN; }
+        PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, NP, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, out, NP, NN, x, w.eerr, s));
+        if (!last) bk[k] = out;
+        if (keep_all) Bt_a = out; else { double* t = Bt_a; Bt_a = Bt_b; Bt_b = t; }
       }
+      if (keep_all) PFML_TRY(chain_sum(B, NP, lb - 1, bk, B11, gv(0), sg, w.m.Wk, CBs, s));
     } else {
       GemmP g;
       g.lda = g.ldb = g.ldd = NP; g.sA = g.sB = g.sD = NN;
@@ -409,8 +418,10 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       }
     }
     // const_l1~ = CB + B11 -> Wk (to be inverted);  const~ = I + m~ (G_0 CB) -> spare (to be inverted)
-    PFML_TRY(add_mat(B, NN, CB, B11, w.m.Wk, s));
-    PFML_TRY(row_scale(B, NP, NP, NP, NN, CB, gv(0), sg, CBs, NP, NN, s));
+    if (!keep_all) {
+      PFML_TRY(add_mat(B, NN, CB, B11, w.m.Wk, s));
+      PFML_TRY(row_scale(B, NP, NP, NP, NN, CB, gv(0), sg, CBs, NP, NN, s));
+    }
     if (emu_nn) {
       PFML_TRY(emu_slice_a(mt, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
       emu_a_cur = mt;                    // the Horner products below reuse these slices of m~
