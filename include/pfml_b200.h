@@ -151,9 +151,10 @@ int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alp
                        void* stream);
 
 /* The same product on the INT8 tensor cores: D = alpha * A B + beta * D with A [M][K], B [K][N] row-major, computed as
- * 28 exact int8 x int8 -> int32 products of seven 7-bit slices per operand (tcgen05.mma kind::i8, accumulators in
- * TMEM, operands staged by bulk-TMA copies) and recombined exactly in int64, then FP64: error <= ~2^-42 of
- * max_k|a_ik| max_k|b_kj| K per element, measured 1e-13 relative to the DMMA product at K = 512 (no reference
+ * 28 exact int8 x int8 -> int32 products of seven balanced base-256 digits per operand (tcgen05.mma kind::i8,
+ * accumulators in TMEM, operands staged by bulk-TMA copies) and recombined exactly in int64, then FP64: 54 bits
+ * below the largest element of each row of A / column of B are kept, measured 3e-15 relative to the DMMA product
+ * at K = 512 (no reference
  * counterpart; it is how the date-step runs its n x n x P products).  Needs K % 64 == 0.  status[0] gets bit 3 on an
  * internal time-out, bit 4 if an operand holds NaN/Inf (they cannot be sliced).  pfml_set_emulation(0) makes
  * pfml_date_steps use the DMMA kernel for those products instead (default 1, or env PFML_EMULATE_FP64). */

@@ -1,19 +1,21 @@
 // FP64 GEMM emulated on the INT8 tensor cores of sm_100a: tcgen05.mma kind::i8, accumulators in TMEM, operands
 // staged by bulk TMA copies (cp.async.bulk + mbarrier), Ozaki-style error-free slicing.
 //
-//   a_ik = 2^ea_i sum_{t<S} qa_t 2^(-7(t+1)),   b_kj = 2^eb_j sum_{t<S} qb_t 2^(-7(t+1)),   q in [-127, 127], S = 8
-//   C_ij = 2^(ea_i + eb_j) sum_{d<S} 2^(-7(d+2)) X_d,   X_d = sum_{i+j=d} qa_i . qb_j   (EXACT int32: K 127^2 S < 2^31)
+//   a_ik = 2^(ea_i + 2) sum_{t<S} da_t 256^-(t+1),   b_kj = 2^(eb_j + 2) sum_{t<S} db_t 256^-(t+1),   d in [-128, 127]
+//   (balanced base-256 digits of round(x 2^(8 S - 2 - e)); S = 7 slices carry 54 bits)
+//   C_ij = 2^(ea_i + eb_j - 12) sum_{d<S} 256^-d X_d,   X_d = sum_{i+j=d} da_i . db_j   (EXACT int32: K 128^2 S < 2^31)
 //
-// Only the slice pairs with i + j < S are multiplied (36 products); the dropped ones are below
-// 2^-56 S K |a|_rowmax |b|_colmax, i.e. the result is as accurate as a native FP64 GEMM (measured: error 4e-16 of
-// sum_k |a_ik b_kj|).  Why it pays: the DMMA pipe peaks at 37 TFLOP/s, the INT8 pipe at 4.5 POP/s; 36 INT8 products
-// per FP64 product still leave > 60 FP64-equivalent TFLOP/s.
+// Only the slice pairs with i + j < S are multiplied (28 products for S = 7); the dropped ones are below
+// 2^-58 of |a|_rowmax |b|_colmax per term and carry no systematic sign, so the result is as accurate as a native FP64
+// GEMM (measured against the DMMA kernel in tests/test_emulated_gemm_gpu.py).  Why it pays: the DMMA pipe peaks at
+// 37 TFLOP/s, the INT8 pipe at 4.5 POP/s; 28 INT8 products per FP64 product still leave > 60 FP64-equivalent TFLOP/s.
 //
 // Layout: slices are written to global memory already in the shared-memory order the UMMA descriptors expect
 // (K-major, no swizzle, 8 rows x 16 B core matrices), one contiguous block per (row block, 64-byte k chunk, all
 // slices), so a pipeline stage is ONE bulk copy per operand.  One CTA per SM walks the output tiles (128 x 64);
-// the 8 accumulators X_d occupy all 512 TMEM columns.  Warp 0: TMA producer; warp 1: MMA issuer; warp 2: TMEM
-// allocator; warps 4-7: epilogue (TMEM -> registers, exact int64 recombination, scaling, fused row scale / addend).
+// the S accumulators X_d occupy S x 64 of the 512 TMEM columns.  Warp 0: TMA producer; warp 1: MMA issuer; warp 2:
+// TMEM allocator; warps 4-19: epilogue (TMEM -> registers, exact int64 recombination, scaling through the exponent
+// field, fused row / column scale, addend, identity, second output; stores transposed through shared memory).
 #include <cstdlib>
 
 #include "common.cuh"
@@ -30,34 +32,39 @@ constexpr int EBM = 128, EBN = 64, EKC = 64;                 // CTA tile, k chun
 constexpr int ELBO = 128, ESBO = (EKC / 16) * 128;           // canonical layout strides (bytes)
 constexpr int EA_STAGE = ES * EBM * EKC, EB_STAGE = ES * EBN * EKC;   // 64 KB, 32 KB
 constexpr int ESTAGES = 2;
+constexpr double kBScale = 1.0 / 4096.0;                     // a b = 2^(ea + eb - 12) sum_d acc_d 2^(-8 d): folded into the B scales
 
 __host__ __device__ inline int canon(int r, int kk) { return (r % 8) * 16 + (r / 8) * ESBO + (kk / 16) * ELBO + kk % 16; }
 
-// 16 values -> ES signed 7-bit slices each, in the integer domain: |x| 2^-e = 0.f1 f2 ... (7-bit fields), the fields
-// are cut out of the 53-bit significand with shifts (truncation toward zero), the sign is applied per field.
-// e is the block exponent (|x| < 2^e); zeros, denormals and values below 2^(e - 7 ES) give all-zero slices.
+// 16 values -> ES balanced base-256 digits each: F = round(x 2^(8 ES - 2 - e)) as a signed integer (|x| < 2^e, so
+// |F| <= 2^(8 ES - 2)), F = sum_t d_t 256^(ES-1-t) with d_t in [-128, 127] taken from the bottom (the top digit stays
+// within +-65).  Every slice carries 8 bits, 8 ES - 2 bits in all (54 for ES = 7: the whole FP64 significand of the
+// largest element of the row / column); the digit signs are not tied to the sign of x, so the products left out
+// (i + j >= ES) have no systematic sign.  Zeros, denormals and values below 2^(e - 8 ES + 1) give all-zero slices.
 __device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* dst, long slice_stride) {
-  unsigned long long f[16];
-  bool neg[16];
+  long long f[16];
 #pragma unroll
   for (int k = 0; k < 16; k++) {
     const long long bits = __double_as_longlong(x[k]);
     const int ex = (int)((bits >> 52) & 0x7ff);
     const unsigned long long mant = ((unsigned long long)bits & 0xFFFFFFFFFFFFFull) | (ex ? (1ull << 52) : 0ull);
-    const int sh = 1075 + e - 7 * ES - ex;                 // F = floor(|x| 2^(7 ES - e)) = mant >> sh
-    f[k] = (ex == 0 || sh >= 64) ? 0ull : (sh >= 0 ? (mant >> sh) : (mant << (-sh)));
-    neg[k] = bits < 0;
+    const int sh = 1075 + e - (8 * ES - 2) - ex;           // |F| = round(mant 2^-sh)
+    const unsigned long long fv = (ex == 0 || sh >= 64) ? 0ull : (sh > 0 ? ((mant + (1ull << (sh - 1))) >> sh) : (mant << (-sh)));
+    f[k] = bits < 0 ? -(long long)fv : (long long)fv;
   }
+  union U { int8_t b[16]; int4 v; };
+  U u[ES];
 #pragma unroll
-  for (int t = 0; t < ES; t++) {
-    union { int8_t b[16]; int4 v; } u;
+  for (int t = ES - 1; t >= 0; t--) {
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-      const int q = (int)((f[k] >> (7 * (ES - 1 - t))) & 127ull);
-      u.b[k] = (int8_t)(neg[k] ? -q : q);
+      const int8_t d = (int8_t)(f[k] & 0xff);
+      u[t].b[k] = d;
+      f[k] = (f[k] - (long long)d) >> 8;
     }
-    *reinterpret_cast<int4*>(dst + t * slice_stride) = u.v;
   }
+#pragma unroll
+  for (int t = 0; t < ES; t++) *reinterpret_cast<int4*>(dst + t * slice_stride) = u[t].v;
 }
 
 // A-type operand: X [R][K] with K contiguous (ld), scaled per row, blocks of BR rows (128 for A, 64 for B^T operands).
@@ -227,7 +234,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 
 
 struct EmuP {
-  const int8_t* As; const int8_t* Bs; const double* sa; const double* sb;   // slices and 2^e scales (sb includes 2^-14)
+  const int8_t* As; const int8_t* Bs; const double* sa; const double* sb;   // slices and 2^e scales (sb includes 2^-12)
   double* D; long ldd, sD;
   const double* E; long lde, sE;
   const double* rs; long s_rs;
@@ -337,7 +344,8 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
     const int q = warp & 3, g = (warp - 4) >> 2;
     double* stg = reinterpret_cast<double*>(smem + ESTAGES * (EA_STAGE + EB_STAGE)) + (warp - 4) * (32 * 9);   // 32 x 8 (+1 pad)
     constexpr int GC = EBN / EPI_G;                 // columns per warp
-    const int shl = p.q - 21, shr = 7 * (ES - 1) - p.q;
+    const int shl = p.q - 24, shr = 8 * (ES - 1) - p.q;
+    const long long rnd = shr > 0 ? (1ll << (shr - 1)) : 0;   // round the dropped low bits to nearest
     int tl = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x, tl++) {
       const int nb = (int)(t % p.NB), mb = (int)((t / p.NB) % p.MB), z = (int)(t / ((long)p.NB * p.MB));
@@ -371,12 +379,12 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
           long long hi = 0, lo = 0;
 #pragma unroll
           for (int d = 0; d < ES; d++) {
-            if (d < 4) hi = hi * 128 + (long long)(int32_t)v[d][c];
-            else lo = lo * 128 + (long long)(int32_t)v[d][c];
+            if (d < 4) hi = hi * 256 + (long long)(int32_t)v[d][c];
+            else lo = lo * 256 + (long long)(int32_t)v[d][c];
           }
-          // S = V 2^q with V = sum_d acc_d 2^(-7 d): the bits of the low slices below 2^-q are dropped (q is chosen from K
-          // so that S fits 63 bits; the dropped part is < 2^(-q-14) of max|a| max|b|, below the slicing error)
-          S[c0 + c] = (hi << shl) + (lo >> shr);
+          // S = V 2^q with V = sum_d acc_d 2^(-8 d): the bits of the low slices below 2^-q are dropped (q is chosen from K
+          // so that S fits 63 bits; the dropped part is < 2^(-q-12) of max|a| max|b|, below the slicing error)
+          S[c0 + c] = (hi << shl) + ((lo + rnd) >> shr);
         }
       }
       // phase 2 (overlaps the next tile's products): scale, then store through a per-warp transpose in shared memory so
@@ -430,7 +438,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
 size_t emu_a_slices_bytes(int batch, int M, int K) { return (size_t)batch * ceil_div(M, EBM) * (K / EKC) * (size_t)EA_STAGE; }
 size_t emu_b_slices_bytes(int batch, int K, int N) { return (size_t)batch * ceil_div(N, EBN) * (K / EKC) * (size_t)EB_STAGE; }
 
-bool emu_shape_ok(int M, int N, int K) { return M > 0 && N > 0 && K >= EKC && K % EKC == 0 && (long)K * 127 * 127 * ES < (1L << 31); }
+bool emu_shape_ok(int M, int N, int K) { return M > 0 && N > 0 && K >= EKC && K % EKC == 0 && (long)K * 128 * 128 * ES < (1L << 31); }
 
 // A [M][K] (K contiguous) -> slices + row scales 2^ea
 int emu_slice_a(const double* A, long lda, long sA, int M, int K, int batch, int8_t* out, double* scale, int* err, cudaStream_t s) {
@@ -448,12 +456,12 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
                 cudaStream_t s) {
   if (K == 512) {
     // 64-column blocks are written by two CTAs of 32 columns; the padded half of the last block must be zero-filled too
-    slice_nmajor512_kernel<<<dim3(2 * ceil_div(N, EBN), batch), 512, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, 6.103515625e-05,
+    slice_nmajor512_kernel<<<dim3(2 * ceil_div(N, EBN), batch), 512, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, kBScale,
                                                                              out, err);
     PFML_CHECK_LAUNCH();
     return 0;
   }
-  col_exponent_kernel<<<dim3(ceil_div(N, 128), batch), 128, 0, s>>>(B, ldb, sB, K, N, ex, scale, 6.103515625e-05, err);
+  col_exponent_kernel<<<dim3(ceil_div(N, 128), batch), 128, 0, s>>>(B, ldb, sB, K, N, ex, scale, kBScale, err);
   PFML_CHECK_LAUNCH();
   slice_nmajor_kernel<<<dim3(ceil_div(N, EBN), K / EKC, batch), 256, 0, s>>>(B, ldb, sB, K, N, ceil_div(N, EBN), ex, out);
   PFML_CHECK_LAUNCH();
@@ -479,7 +487,11 @@ int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const doubl
   p.rs = rs; p.s_rs = s_rs; p.alpha = alpha; p.beta = beta; p.M = M; p.N = N; p.K = K;
   p.MB = ceil_div(M, EBM); p.NB = ceil_div(N, EBN); p.batch = batch; p.err = err;
   p.cs = x.cs; p.s_cs = x.s_cs; p.diag = x.diag; p.D2 = x.D2; p.E2 = x.E2; p.ld2 = x.ld2; p.s2 = x.s2;
-  p.q = K <= 512 ? 38 : 33;               // |V| < 1.02 K 127^2: 2^23.1 (K <= 512), 2^28.1 (K <= 16640)
+  // |V| = |sum_d acc_d 2^(-8 d)| < 1.01 K 128^2 < 2^vb: the fixed-point position q leaves one spare bit below the sign
+  int vb = 0;
+  while ((1.01 * K * 16384.0) >= (double)(1ll << vb)) vb++;
+  p.q = 62 - vb;
+  if (p.q > 8 * (ES - 1)) p.q = 8 * (ES - 1);
   constexpr size_t smem = (size_t)ESTAGES * (EA_STAGE + EB_STAGE) + (size_t)(4 * EPI_G) * 32 * 9 * sizeof(double);
   static bool cfg[64] = {};
   static int n_sm[64] = {};

@@ -6,7 +6,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-TOL = 1e-11   # relative to sum_k |a_ik| |b_kj|: 7 slices keep 49 bits per operand below the row / column maximum
+TOL = 1e-13   # relative to sum_k |a_ik| |b_kj|: 7 balanced base-256 slices keep 54 bits below the row / column maximum
 
 
 def _rel(got, A, B, want):
@@ -87,4 +87,4 @@ def test_date_steps_same_with_and_without_emulation():
     for x, y in zip(a, b):
         assert x["status"] == 0 and y["status"] == 0
         for key in ("r_tilde", "denom", "risk", "tc", "signal_t"):
-            assert relerr(x[key], y[key]) < 1e-10, key
+            assert relerr(x[key], y[key]) < 1e-11, key

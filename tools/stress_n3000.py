@@ -16,3 +16,9 @@ st = r.status.cpu().numpy(); d = r.denom[0].cpu().numpy(); ri = r.risk[0].cpu().
 ev = np.linalg.eigvalsh(d)
 print(f"{B} date-steps in {dt*1e3:.1f} ms = {B/dt:.1f} date-steps/s; status {st.tolist()}; symmetric {bool((d == d.T).all())}; "
       f"risk+tc==denom {float(np.abs(ri + tc - d).max() / np.abs(d).max()):.1e}; min eig / max eig {ev.min() / ev.max():.2e}; finite {bool(np.isfinite(d).all())}")
+lib = importlib.import_module(PKG + "._lib").load()
+lib.pfml_set_emulation(0)
+r.run(); torch.cuda.synchronize()
+t0 = time.perf_counter(); r.run(); torch.cuda.synchronize(); dt0 = time.perf_counter() - t0
+d0 = r.denom[0].cpu().numpy(); lib.pfml_set_emulation(1)
+print(f"DMMA path: {B/dt0:.1f} date-steps/s; INT8-emulated vs DMMA denom: {float(np.abs(d - d0).max() / np.abs(d0).max()):.2e} relative")
