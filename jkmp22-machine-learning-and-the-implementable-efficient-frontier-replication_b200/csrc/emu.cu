@@ -223,6 +223,13 @@ __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t da, uint64_t d
   asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n"
                ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void umma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}\n"
+               ::"r"(d_tmem), "r"(a_tmem), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void utccp_128x32(uint32_t d_tmem, uint64_t src_desc) {   // 128 rows x 32 bytes, smem -> TMEM
+  asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(d_tmem), "l"(src_desc) : "memory");
+}
 __device__ __forceinline__ bool elect_one() {      // one lane of a converged warp; lets ptxas issue the tensor ops without a per-lane loop
   uint32_t pred = 0;
   asm volatile("{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\telect.sync rx|px, %1;\n\t@px mov.s32 %0, 1;\n\t}\n" : "+r"(pred) : "r"(0xFFFFFFFFu));
@@ -232,6 +239,13 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
+
+#ifndef PFML_EMU_TS_SLICES
+#define PFML_EMU_TS_SLICES 3
+#endif
+constexpr int ETS = PFML_EMU_TS_SLICES;                      // leading A slices held in TMEM (TS-form products)
+constexpr int EACOL = ES * EBN;                               // their TMEM columns (8 per slice), after the accumulators
+static_assert(EACOL + ETS * 8 <= 512 && ETS <= ES, "TMEM: accumulators + A slices");
 
 struct EmuP {
   const int8_t* As; const int8_t* Bs; const double* sa; const double* sb;   // slices and 2^e scales (sb includes 2^-12)
@@ -311,24 +325,39 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
         asm volatile("tcgen05.fence::after_thread_sync;");
         const uint64_t da0 = make_desc(smem_u32(sA + s * EA_STAGE)), db0 = make_desc(smem_u32(sB + s * EB_STAGE));
         if (elect_one()) {
+        // Per 32-byte k slab.  The first ETS slices of A (used by 7, 6, 5 products) are first copied to TMEM
+        // (tcgen05.cp, executes in issue order with the products) and their products read only B from shared memory;
+        // the other slices are read from shared memory by each product.  A copy costs about as much as 4 products'
+        // worth of A reads, so it pays only for the most reused slices (all-TMEM and all-shared measured equal).
         if (kc == 0) {
 #pragma unroll
-          for (int i = 0; i < ES; i++)
+          for (int kk = 0; kk < EKC / 32; kk++) {
 #pragma unroll
-            for (int j = 0; j < ES - i; j++)
+            for (int i = 0; i < ETS; i++) utccp_128x32(tbase + EACOL + i * 8, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4));
 #pragma unroll
-              for (int kk = 0; kk < EKC / 32; kk++)
-                umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
-                        db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, (kk > 0 || i > 0) ? 1u : 0u);
+            for (int i = 0; i < ES; i++)
+#pragma unroll
+              for (int j = 0; j < ES - i; j++) {
+                const uint32_t acc = (kk > 0 || i > 0) ? 1u : 0u;
+                if (i < ETS) umma_i8_ts(tbase + (i + j) * EBN, tbase + EACOL + i * 8, db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, acc);
+                else umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
+                             db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, acc);
+              }
+          }
         } else {
 #pragma unroll
-          for (int i = 0; i < ES; i++)
+          for (int kk = 0; kk < EKC / 32; kk++) {
 #pragma unroll
-            for (int j = 0; j < ES - i; j++)
+            for (int i = 0; i < ETS; i++) utccp_128x32(tbase + EACOL + i * 8, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4));
 #pragma unroll
-              for (int kk = 0; kk < EKC / 32; kk++)
-                umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
-                        db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, 1u);
+            for (int i = 0; i < ES; i++)
+#pragma unroll
+              for (int j = 0; j < ES - i; j++) {
+                if (i < ETS) umma_i8_ts(tbase + (i + j) * EBN, tbase + EACOL + i * 8, db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, 1u);
+                else umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
+                             db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, 1u);
+              }
+          }
         }
         umma_commit(smem_u32(&empty_bar[s]));
         }

@@ -16,12 +16,14 @@ using namespace pfml;
 
 namespace {
 
+constexpr int MAX_CS = 4;           // compute streams (chunks in flight)
+
 struct Arena {
   void* base = nullptr;
   size_t cap = 0;
-  cudaStream_t compute = nullptr, compute2 = nullptr, copy = nullptr;
+  cudaStream_t compute[MAX_CS] = {}, copy = nullptr;
   cudaEvent_t panel_ready = nullptr;
-  cudaEvent_t computed[2] = {nullptr, nullptr}, drained[2] = {nullptr, nullptr};
+  cudaEvent_t computed[MAX_CS] = {}, drained[MAX_CS] = {};
   bool init = false;
 };
 Arena g_arena[64];
@@ -43,12 +45,12 @@ struct HostPlan {
   unsigned char* has;
   int *date_t, *sel, *n_sel, *status;
   double* stage[2];
-  void* ws[2];
+  void* ws[MAX_CS];
   size_t ws_bytes, stage_doubles, total;
 };
 
 HostPlan plan(void* base, const pfml_host_block_t* b, int B, int NP, int chunk, bool want_risk, bool want_tc, bool want_sig,
-              size_t ws_bytes) {
+              size_t ws_bytes, int n_cs) {
   HostPlan h{};
   Bump m(base);
   const size_t TN = (size_t)b->T * b->N, P = b->p + 1;
@@ -69,8 +71,7 @@ HostPlan plan(void* base, const pfml_host_block_t* b, int B, int NP, int chunk, 
   h.stage[0] = m.take<double>(h.stage_doubles);
   h.stage[1] = nullptr;
   h.ws_bytes = ws_bytes;
-  h.ws[0] = m.take<char>(ws_bytes);
-  h.ws[1] = m.take<char>(ws_bytes);
+  for (int i = 0; i < n_cs; i++) h.ws[i] = m.take<char>(ws_bytes);
   h.total = m.off;
   return h;
 }
@@ -113,32 +114,33 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
   PFML_CUDA_OK(cudaSetDevice(device));
   Arena& a = g_arena[device];
   if (!a.init) {
-    PFML_CUDA_OK(cudaStreamCreateWithFlags(&a.compute, cudaStreamNonBlocking));
-    PFML_CUDA_OK(cudaStreamCreateWithFlags(&a.compute2, cudaStreamNonBlocking));
     PFML_CUDA_OK(cudaStreamCreateWithFlags(&a.copy, cudaStreamNonBlocking));
     PFML_CUDA_OK(cudaEventCreateWithFlags(&a.panel_ready, cudaEventDisableTiming));
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < MAX_CS; i++) {
+      PFML_CUDA_OK(cudaStreamCreateWithFlags(&a.compute[i], cudaStreamNonBlocking));
       PFML_CUDA_OK(cudaEventCreateWithFlags(&a.computed[i], cudaEventDisableTiming));
       PFML_CUDA_OK(cudaEventCreateWithFlags(&a.drained[i], cudaEventDisableTiming));
     }
     a.init = true;
   }
+  static const int env_cs = getenv("PFML_HOST_STREAMS") ? atoi(getenv("PFML_HOST_STREAMS")) : 2;   // tuning aid
+  const int n_cs = env_cs < 1 ? 1 : (env_cs > MAX_CS ? MAX_CS : env_cs);
   const int NP = pfml_padded_n(n_max);
   const size_t TN = (size_t)blk->T * blk->N, P = blk->p + 1;
   pfml_panel_t pan{};
   pan.T = blk->T; pan.N = blk->N; pan.F = blk->F; pan.p = blk->p; pan.K = blk->K;
   pan.gamma_rel = blk->gamma_rel; pan.mu = blk->mu; pan.lb = blk->lb; pan.iterations = blk->iterations;
   const size_t ws_bytes = pfml_date_steps_workspace_bytes(&pan, chunk, n_max);
-  HostPlan h = plan(nullptr, blk, B, NP, chunk, risk != nullptr, tc != nullptr, signal_t != nullptr, ws_bytes);
+  HostPlan h = plan(nullptr, blk, B, NP, chunk, risk != nullptr, tc != nullptr, signal_t != nullptr, ws_bytes, n_cs);
   if (h.total > a.cap) {
     if (a.base) PFML_CUDA_OK(cudaFree(a.base));
     a.base = nullptr; a.cap = 0;
     PFML_CUDA_OK(cudaMalloc(&a.base, h.total));
     a.cap = h.total;
   }
-  h = plan(a.base, blk, B, NP, chunk, risk != nullptr, tc != nullptr, signal_t != nullptr, ws_bytes);
-  cudaStream_t cs = a.compute, ds = a.copy;
-  cudaStream_t cstream[2] = {a.compute, a.compute2};
+  h = plan(a.base, blk, B, NP, chunk, risk != nullptr, tc != nullptr, signal_t != nullptr, ws_bytes, n_cs);
+  cudaStream_t cs = a.compute[0], ds = a.copy;
+  cudaStream_t* cstream = a.compute;
 
   // ---- upload the block ---------------------------------------------------------------------------
 #define H2D(dst, src, count, type) PFML_CUDA_OK(cudaMemcpyAsync(dst, src, (size_t)(count) * sizeof(type), cudaMemcpyHostToDevice, cs))
@@ -167,7 +169,7 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
   pan.fct_load = h.fct_load; pan.fct_cov = h.fct_cov; pan.ivol = h.ivol; pan.wealth = h.wealth; pan.rf = h.rf;
 
   PFML_CUDA_OK(cudaEventRecord(a.panel_ready, cs));
-  PFML_CUDA_OK(cudaStreamWaitEvent(a.compute2, a.panel_ready, 0));
+  for (int i = 1; i < n_cs; i++) PFML_CUDA_OK(cudaStreamWaitEvent(a.compute[i], a.panel_ready, 0));
   // ---- chunks: compute on two alternating streams, drain on `ds` -----------------------------------
   const int n_chunks = (int)sched.size();
   const bool trace = getenv("PFML_HOST_TRACE") != nullptr;
@@ -176,7 +178,7 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
   mark(cs);
   int b0 = 0;
   for (int c = 0; c < n_chunks; b0 += sched[c], c++) {
-    const int nb = sched[c], sb = c & 1;
+    const int nb = sched[c], sb = c % n_cs;
     double* st = h.stage[0];
     double* d_rt = st + (size_t)b0 * P;                     st += (size_t)B * P;
     double* d_den = st + (size_t)b0 * P * P;                st += (size_t)B * P * P;
@@ -199,8 +201,7 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
     PFML_CUDA_OK(cudaEventRecord(a.drained[sb], ds));
     mark(ds);
   }
-  PFML_CUDA_OK(cudaStreamSynchronize(a.compute));
-  PFML_CUDA_OK(cudaStreamSynchronize(a.compute2));
+  for (int i = 0; i < n_cs; i++) PFML_CUDA_OK(cudaStreamSynchronize(a.compute[i]));
   if (status) PFML_CUDA_OK(cudaMemcpyAsync(status, h.status, sizeof(int) * B, cudaMemcpyDeviceToHost, ds));
   PFML_CUDA_OK(cudaStreamSynchronize(ds));
   if (trace) {
