@@ -80,7 +80,11 @@ struct EmuExtra {
   const double* cs = nullptr; long s_cs = 0;
   double diag = 0.0;
   double* D2 = nullptr; const double* E2 = nullptr; long ld2 = 0, s2 = 0;
+  const double* az = nullptr; long s_az = 0;   // per-matrix factor on alpha
+  bool sym = false;                            // symmetric result: only the upper triangle is written, the caller mirrors it
 };
+int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
+                        double* sa, int* err, cudaStream_t s);
 int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
                const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD,
                const EmuExtra& x, int* err, cudaStream_t s);

@@ -41,7 +41,8 @@ __host__ __device__ inline int canon(int r, int kk) { return (r % 8) * 16 + (r /
 // within +-65).  Every slice carries 8 bits, 8 ES - 2 bits in all (54 for ES = 7: the whole FP64 significand of the
 // largest element of the row / column); the digit signs are not tied to the sign of x, so the products left out
 // (i + j >= ES) have no systematic sign.  Zeros, denormals and values below 2^(e - 8 ES + 1) give all-zero slices.
-__device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* dst, long slice_stride) {
+__device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* dst, long slice_stride, int8_t* dst2 = nullptr,
+                                        long slice_stride2 = 0) {
   long long f[16];
 #pragma unroll
   for (int k = 0; k < 16; k++) {
@@ -64,7 +65,14 @@ __device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* ds
     }
   }
 #pragma unroll
-  for (int t = 0; t < ES; t++) *reinterpret_cast<int4*>(dst + t * slice_stride) = u[t].v;
+  if (dst) {
+#pragma unroll
+    for (int t = 0; t < ES; t++) *reinterpret_cast<int4*>(dst + t * slice_stride) = u[t].v;
+  }
+  if (dst2) {
+#pragma unroll
+    for (int t = 0; t < ES; t++) *reinterpret_cast<int4*>(dst2 + t * slice_stride2) = u[t].v;
+  }
 }
 
 // A-type operand: X [R][K] with K contiguous (ld), scaled per row, blocks of BR rows (128 for A, 64 for B^T operands).
@@ -159,11 +167,13 @@ slice_nmajor_kernel(const double* __restrict__ X, long ld, long sX, int K, int C
   slice16(x, e, base + canon(nn, kq * 16), (long)EBN * EKC);
 }
 
-// B-type operand with K == 512 in one pass: a CTA owns 32 columns x all 512 k (thread = column, 32 consecutive k held
-// in registers), the column maxima go through shared memory, no separate exponent kernel.
+// N-major operand X [512][C] in one pass: a CTA owns 32 columns x all 512 k (thread = column, 32 consecutive k held in
+// registers), the column maxima go through shared memory, no separate exponent kernel.  Writes the B-type slices
+// (64-column blocks, `out`) and / or the A-type slices of X' (128-row blocks, `outA`: X' as the left operand).
 __global__ void __launch_bounds__(512, 1)
 slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, int CB, int* __restrict__ ex, double* __restrict__ scale,
-                       double extra, int8_t* __restrict__ out, int* __restrict__ err) {
+                       double extra, int8_t* __restrict__ out, int RBA, double* __restrict__ scaleA, int8_t* __restrict__ outA,
+                       int* __restrict__ err) {
   constexpr int K = 512, KB = K / EKC;
   __shared__ double red[16][33];
   const int z = blockIdx.y, lane = threadIdx.x & 31, kq = threadIdx.x >> 5;
@@ -188,17 +198,18 @@ slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, in
   for (int j = 0; j < 16; j++) mx = fmax(mx, red[j][lane]);
   const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
   if (kq == 0 && n < C) {
-    ex[(long)z * C + n] = e;
-    scale[(long)z * C + n] = scalbn(extra, e);
+    if (out) { ex[(long)z * C + n] = e; scale[(long)z * C + n] = scalbn(extra, e); }
+    if (outA) scaleA[(long)z * C + n] = scalbn(1.0, e);
   }
-  if (cb >= CB) return;
-  int8_t* base = out + (((long)z * CB + cb) * KB + kq / 2) * (long)EB_STAGE;
+  int8_t* base = (out && cb < CB) ? out + (((long)z * CB + cb) * KB + kq / 2) * (long)EB_STAGE : nullptr;
+  int8_t* baseA = (outA && n / EBM < RBA) ? outA + (((long)z * RBA + n / EBM) * KB + kq / 2) * (long)EA_STAGE : nullptr;
 #pragma unroll
   for (int h = 0; h < 2; h++) {
     double y[16];
 #pragma unroll
     for (int j = 0; j < 16; j++) y[j] = x[h * 16 + j];
-    slice16(y, e, base + canon(nn, (kq & 1) * 32 + h * 16), (long)EBN * EKC);
+    const int kk = (kq & 1) * 32 + h * 16;
+    slice16(y, e, base ? base + canon(nn, kk) : nullptr, (long)EBN * EKC, baseA ? baseA + canon(n % EBM, kk) : nullptr, (long)EBM * EKC);
   }
 }
 
@@ -255,6 +266,8 @@ struct EmuP {
   double alpha, beta;
   int M, N, K, MB, NB, batch;
   const double* cs; long s_cs; double diag;
+  const double* az; long s_az;              // per-matrix factor on alpha (batch stride s_az)
+  int sym;                                  // symmetric result: only the upper triangle is produced (the caller mirrors it)
   double* D2; const double* E2; long ld2, s2;
   int q;                                   // fixed-point position of the recombined sum (see the epilogue)
   int* err;
@@ -295,6 +308,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
     long it = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
       const int nb = (int)(t % p.NB), mb = (int)((t / p.NB) % p.MB), z = (int)(t / ((long)p.NB * p.MB));
+      if (p.sym && nb * EBN + EBN - 1 < mb * EBM) continue;          // tile strictly below the diagonal
       const int8_t* a_src = p.As + (((long)z * p.MB + mb) * KB) * (long)EA_STAGE;
       const int8_t* b_src = p.Bs + (((long)z * p.NB + nb) * KB) * (long)EB_STAGE;
       for (int kc = 0; kc < KB; kc++, it++) {
@@ -316,7 +330,8 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
     const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(EBN >> 3) << 17) | ((uint32_t)(EBM >> 4) << 24);
     long it = 0;
     int tl = 0;
-    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x, tl++) {
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      if (p.sym && (int)(t % p.NB) * EBN + EBN - 1 < (int)((t / p.NB) % p.MB) * EBM) continue;
       if (!mbar_wait(smem_u32(&acc_empty), (uint32_t)((tl & 1) ^ 1))) { atomicOr(p.err, 4); return; }   // epilogue drained TMEM
       asm volatile("tcgen05.fence::after_thread_sync;");
       for (int kc = 0; kc < KB; kc++, it++) {
@@ -365,6 +380,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
       }
       if (elect_one()) umma_commit(smem_u32(&acc_full));
       __syncwarp();
+      tl++;
     }
   } else if (warp >= 4) {
     // ===== epilogue: EPI_WARPS warps, warp = (lane quarter q of TMEM, column group g of EBN / EPI_G columns) =====
@@ -376,13 +392,15 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
     const int shl = p.q - 24, shr = 8 * (ES - 1) - p.q;
     const long long rnd = shr > 0 ? (1ll << (shr - 1)) : 0;   // round the dropped low bits to nearest
     int tl = 0;
-    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x, tl++) {
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
       const int nb = (int)(t % p.NB), mb = (int)((t / p.NB) % p.MB), z = (int)(t / ((long)p.NB * p.MB));
+      if (p.sym && nb * EBN + EBN - 1 < mb * EBM) continue;
       const int row = mb * EBM + q * 32 + lane;
       const bool rok = row < p.M;
       // the operand scales are powers of two: they go into the exponent field instead of FP64 multiplies
       const int ea = rok ? (int)((__double_as_longlong(p.sa[(long)z * p.M + row]) >> 52) & 0x7ff) - 1023 - p.q : 0;
       double rsv = rok ? p.alpha : 0.0;
+      if (p.az) rsv *= p.az[(long)z * p.s_az];
       if (p.rs && rok) rsv *= p.rs[(long)z * p.s_rs + row];
       const int colbase = nb * EBN + g * GC;
       const double* sbz = p.sb + (long)z * p.N + colbase;
@@ -439,7 +457,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
 #pragma unroll
           for (int i = 0; i < 8; i++) {
             const int r = mb * EBM + q * 32 + i * 4 + rr;
-            if (r < p.M) {
+            if (r < p.M && !(p.sym && r > col)) {           // symmetric: only the upper triangle is produced, then mirrored
               double o = stg[(i * 4 + rr) * 9 + cc];
               if (p.E) o += p.beta * p.E[(long)z * p.sE + (long)r * p.lde + col];
               o *= csv;
@@ -454,6 +472,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
         }
         __syncwarp();
       }
+      tl++;
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;");
@@ -486,13 +505,23 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
   if (K == 512) {
     // 64-column blocks are written by two CTAs of 32 columns; the padded half of the last block must be zero-filled too
     slice_nmajor512_kernel<<<dim3(2 * ceil_div(N, EBN), batch), 512, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, kBScale,
-                                                                             out, err);
+                                                                             out, 0, nullptr, nullptr, err);
     PFML_CHECK_LAUNCH();
     return 0;
   }
   col_exponent_kernel<<<dim3(ceil_div(N, 128), batch), 128, 0, s>>>(B, ldb, sB, K, N, ex, scale, kBScale, err);
   PFML_CHECK_LAUNCH();
   slice_nmajor_kernel<<<dim3(ceil_div(N, EBN), K / EKC, batch), 256, 0, s>>>(B, ldb, sB, K, N, ceil_div(N, EBN), ex, out);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+// X [512][C] (C contiguous) -> B-type slices of X (outB, may be null) and / or A-type slices of X' (outA, may be null)
+int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
+                        double* sa, int* err, cudaStream_t s) {
+  const int CB = ceil_div(C, EBN), RBA = ceil_div(C, EBM);
+  const int blocks = outA ? 4 * RBA : 2 * CB;          // 32 columns per CTA; the padded tail of the last block is zero-filled
+  slice_nmajor512_kernel<<<dim3(blocks, batch), 512, 0, s>>>(X, ld, sX, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err);
   PFML_CHECK_LAUNCH();
   return 0;
 }
@@ -515,7 +544,7 @@ int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const doubl
   p.As = As; p.Bs = Bs; p.sa = sa; p.sb = sb; p.D = D; p.ldd = ldd; p.sD = sD; p.E = E; p.lde = lde; p.sE = sE;
   p.rs = rs; p.s_rs = s_rs; p.alpha = alpha; p.beta = beta; p.M = M; p.N = N; p.K = K;
   p.MB = ceil_div(M, EBM); p.NB = ceil_div(N, EBN); p.batch = batch; p.err = err;
-  p.cs = x.cs; p.s_cs = x.s_cs; p.diag = x.diag; p.D2 = x.D2; p.E2 = x.E2; p.ld2 = x.ld2; p.s2 = x.s2;
+  p.cs = x.cs; p.s_cs = x.s_cs; p.diag = x.diag; p.az = x.az; p.s_az = x.s_az; p.sym = x.sym ? 1 : 0; p.D2 = x.D2; p.E2 = x.E2; p.ld2 = x.ld2; p.s2 = x.s2;
   // |V| = |sum_d acc_d 2^(-8 d)| < 1.01 K 128^2 < 2^vb: the fixed-point position q leaves one spare bit below the sign
   int vb = 0;
   while ((1.01 * K * 16384.0) >= (double)(1ll << vb)) vb++;

@@ -231,6 +231,36 @@ __global__ void chain_sum_kernel(int NP, int nk, ChainPtrs p, const double* __re
   cbs[o] = acc * g0[(long)b * sg + r];
 }
 
+// a9 finish for the upper-triangle products: denom = risk + tc, and risk, tc, denom mirrored into their lower triangles
+// (32 x 32 tiles through shared memory so that both the reads and the transposed writes are coalesced)
+__global__ void sym_finish_kernel(int P, double* __restrict__ risk, double* __restrict__ tc, double* __restrict__ denom) {
+  __shared__ double tr[32][33], tt[32][33];
+  const int bi = blockIdx.y, bj = blockIdx.x;
+  if (bj < bi) return;
+  const long zo = (long)blockIdx.z * P * P;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  for (int k = ty; k < 32; k += 8) {
+    const int r = bi * 32 + k, c = bj * 32 + tx;
+    const bool ok = r < P && c < P;
+    tr[k][tx] = ok ? risk[zo + (long)r * P + c] : 0.0;
+    tt[k][tx] = ok ? tc[zo + (long)r * P + c] : 0.0;
+  }
+  __syncthreads();
+  for (int k = ty; k < 32; k += 8) {
+    // upper tile position (r, c): only elements on / above the diagonal are valid inputs
+    int r = bi * 32 + k, c = bj * 32 + tx;
+    if (r < P && c < P && c >= r) denom[zo + (long)r * P + c] = tr[k][tx] + tt[k][tx];
+    // mirrored position (c', r') = (bj * 32 + k, bi * 32 + tx) takes the value of (bi * 32 + tx, bj * 32 + k)
+    r = bj * 32 + k; c = bi * 32 + tx;
+    if (r < P && c < P && r > c) {
+      const double rv = tr[tx][k], tv = tt[tx][k];
+      risk[zo + (long)r * P + c] = rv;
+      tc[zo + (long)r * P + c] = tv;
+      denom[zo + (long)r * P + c] = rv + tv;
+    }
+  }
+}
+
 // partial Frobenius sums of M, Mi and M - I over a chunk of rows; deterministic two-stage reduction
 __global__ void db_norms_partial_kernel(int NP, const double* __restrict__ M, const double* __restrict__ Mi, double* __restrict__ part) {
   const int b = blockIdx.y, ch = blockIdx.x;
@@ -600,6 +630,13 @@ int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11,
   ChainPtrs p{};
   for (int k = 0; k < nk; k++) p.bk[k] = bk[k];
   chain_sum_kernel<<<grid_rc(NP, NP, B), 128, 0, s>>>(NP, nk, p, b11, g0, sg, wk, cbs);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int sym_finish(int B, int P, double* risk, double* tc, double* denom, cudaStream_t s) {
+  const int nb = ceil_div(P, 32);
+  sym_finish_kernel<<<dim3(nb, nb, B), dim3(32, 8), 0, s>>>(P, risk, tc, denom);
   PFML_CHECK_LAUNCH();
   return 0;
 }

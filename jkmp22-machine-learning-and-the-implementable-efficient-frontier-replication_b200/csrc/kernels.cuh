@@ -62,6 +62,7 @@ int mt0_from_sqrt(int B, int NP, const double* x, const double* Y, double* mt, c
 int fp_build(int B, int NP, const double* x, const double* yv, const double* mt, const double* sgr, double* Wk, cudaStream_t s);
 int chain_init(int B, int NP, const double* mt, const double* g1, long sg, double* Bt, double* CB, cudaStream_t s);
 int add_mat(int B, long n_elem, const double* a, const double* b, double* out, cudaStream_t s);
+int sym_finish(int B, int P, double* risk, double* tc, double* denom, cudaStream_t s);
 int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11, const double* g0, long sg, double* wk, double* cbs,
               cudaStream_t s);
 int row_scale(int B, int rows, int cols, long ld, long stride, const double* in, const double* rsv, long srs, double* out,

@@ -299,10 +299,10 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.OM = c.take<double>((size_t)B * (NP + KP) * w.ldP);
   w.BS = c.take<double>((size_t)B * (NP + KP) * w.ldP);
   w.OMC = c.take<double>(BnP);
-  w.eAs = c.take<int8_t>(emu_a_slices_bytes(B, NP, NP));
-  const int Pn = P > NP ? P : NP;          // B operands are n x P (Horner, solves) or n x n (chain)
+  const int Pn = P > NP ? P : NP;          // B operands are n x P (Horner, solves) or n x n (chain); A operands n x n or P x n (a9)
+  w.eAs = c.take<int8_t>(emu_a_slices_bytes(B, Pn, NP));
   w.eBs = c.take<int8_t>(emu_b_slices_bytes(B, NP, Pn));
-  w.esa = c.take<double>((size_t)B * NP); w.esb = c.take<double>((size_t)B * Pn);
+  w.esa = c.take<double>((size_t)B * Pn); w.esb = c.take<double>((size_t)B * Pn);
   w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64);
   w.chain = nt >= 5 ? c.take<double>((size_t)(nt - 4) * BNN) : nullptr;   // lb - 2 matrices
   w.risk_tmp = need_risk ? c.take<double>((size_t)B * P * P) : nullptr;
@@ -513,6 +513,33 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     PFML_TRY(gemm(f, B, s));
     PFML_TRY(row_scale(B, NP, P, ldP, sStack, w.OM, w.v.dvl, NP, w.BS, ldP, sStack, s));
     // risk = [omega~; Y]' [gamma (ivol/lambda) omega~; gamma F Y]
+    const bool emu_pp = emu && NP == 512 && emu_shape_ok(P, P, NP);   // the one-pass transposed slicing is written for K = 512
+    if (emu_pp) {
+      // factor part (K = KP) on the DMMA pipe, then the n-deep part on the INT8 tensor cores accumulates onto it;
+      // symmetric: only the upper triangle is computed; sym_finish mirrors it and forms denom
+      GemmP r;
+      r.a_kinner = false; r.A = w.OM + (long)NP * ldP; r.lda = ldP; r.sA = sStack;
+      r.B = w.BS + (long)NP * ldP; r.ldb = ldP; r.sB = sStack;
+      r.D = risk; r.ldd = P; r.sD = (long)P * P;
+      r.M = P; r.N = P; r.K = KP; r.sym = 1;
+      PFML_TRY(gemm(r, B, s));
+      PFML_TRY(emu_slice_nmajor512(w.OM, ldP, sStack, P, B, nullptr, nullptr, nullptr, w.eAs, w.esa, w.eerr, s));
+      PFML_TRY(emu_slice_nmajor512(w.BS, ldP, sStack, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s));
+      EmuExtra xr;
+      xr.sym = true;
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 1.0, risk, P, (long)P * P, risk, P, (long)P * P, xr,
+                          w.eerr, s));
+      // tc = w omega~_chg' omega~_chg ; denom = risk + tc
+      PFML_TRY(emu_slice_nmajor512(w.OMC, ldP, nP, P, B, w.eBs, w.esb, w.eex, w.eAs, w.esa, w.eerr, s));
+      EmuExtra xt;
+      xt.sym = true; xt.az = w.v.scal + 0; xt.s_az = NSCAL;
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, tc, P, (long)P * P, xt, w.eerr, s));
+      PFML_TRY(sym_finish(B, P, risk, tc, denom, s));        // denom = risk + tc; lower triangles = copies of the upper
+      if (status) {
+        fold_emu_error_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, w.eerr, status);
+        PFML_CHECK_LAUNCH();
+      }
+    } else {
     GemmP r;
     r.a_kinner = false; r.A = w.OM; r.lda = ldP; r.sA = sStack;
     r.B = w.BS; r.ldb = ldP; r.sB = sStack;
@@ -528,6 +555,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     t.az = w.v.scal + 0; t.s_z = NSCAL;
     t.M = P; t.N = P; t.K = NP; t.sym = 1;
     PFML_TRY(gemm(t, B, s));
+    }
   }
   return 0;
 }
