@@ -436,7 +436,11 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
       }
       // phase 2 (overlaps the next tile's products): scale, then store through a per-warp transpose in shared memory so
       // that one global instruction covers 4 rows x 64 contiguous bytes instead of 32 rows x 8 bytes
+      // One FP64 instruction per element: the power-of-two scales are applied in the exponent field and alpha rs[row]
+      // rides along in the pad column of the staging tile.  (ncu attributes most stall samples of this loop to the
+      // DFMA / DMUL; removing them altogether did not change the kernel time -- the products, not this loop, pace it.)
       const int rr = lane >> 3, cc = lane & 7;
+      stg[lane * 9 + 8] = rsv;
 #pragma unroll
       for (int c0 = 0; c0 < GC; c0 += 8) {
 #pragma unroll
@@ -448,7 +452,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
           // exponent out of range: flush to zero / overflow to infinity (never seen with the panel's magnitudes)
           const int h1 = (S[c0 + c] == 0 || nf <= 0) ? 0 : (nf >= 2047 ? ((h0 & 0x80000000) | 0x7ff00000) : h0 + (e << 20));
           const int l1 = (S[c0 + c] == 0 || nf <= 0 || nf >= 2047) ? 0 : __double2loint(x0);
-          stg[lane * 9 + c] = rsv * __hiloint2double(h1, l1);
+          stg[lane * 9 + c] = __hiloint2double(h1, l1);
         }
         __syncwarp();
         const int col = colbase + c0 + cc;
@@ -458,10 +462,13 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
           for (int i = 0; i < 8; i++) {
             const int r = mb * EBM + q * 32 + i * 4 + rr;
             if (r < p.M && !(p.sym && r > col)) {           // symmetric: only the upper triangle is produced, then mirrored
-              double o = stg[(i * 4 + rr) * 9 + cc];
-              if (p.E) o += p.beta * p.E[(long)z * p.sE + (long)r * p.lde + col];
-              o *= csv;
-              if (r == col) o += p.diag;
+              const double x = stg[(i * 4 + rr) * 9 + cc], rv = stg[(i * 4 + rr) * 9 + 8];
+              double o;
+              if (!p.E) o = rv * x;
+              else if (p.beta == 1.0) o = fma(rv, x, p.E[(long)z * p.sE + (long)r * p.lde + col]);
+              else o = fma(rv, x, p.beta * p.E[(long)z * p.sE + (long)r * p.lde + col]);
+              if (p.cs) o *= csv;
+              if (p.diag != 0.0 && r == col) o += p.diag;
               p.D[(long)z * p.sD + (long)r * p.ldd + col] = o;
               if (p.D2) {
                 const long o2 = (long)z * p.s2 + (long)r * p.ld2 + col;
