@@ -145,13 +145,13 @@ __global__ void build_x_dense_kernel(int n, int NP, const double* __restrict__ s
 // ------------------------------------------------------------------------------------------------
 // Standardise + scale (PFML_Input_Data.py:357-388) for every (date, tau): de-mean each RFF column over the
 // date-d universe (two passes: mean, then sum of squares of the centred column, quirk Q6), l2-normalise,
-// multiply rows by 1/vol_scale, then by sqrt(lambda_i) (tilde domain) and, for tau in 2..lb, by g_{tau-1}
-// (pre-scaled Horner addend).  Output columns are in feat_all order: constant first (quirk Q3/Q4).
+// multiply rows by 1/vol_scale, then by sqrt(lambda_i) (tilde domain) and, if `prescale`, for tau in 2..lb by
+// g_{tau-1} (pre-scaled Horner addend of the DMMA path).  Output columns are in feat_all order: constant first (quirk Q3/Q4).
 // One thread per output column, rows streamed; the slab stays L2-resident between the three passes.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 standardize_kernel(PanelView pv, int NP, int P, long ldP, const int* __restrict__ date_t, const int* __restrict__ sel,
-                   const int* __restrict__ nsel, BatchVecs v, double* __restrict__ St, double* __restrict__ signal_t) {
+                   const int* __restrict__ nsel, BatchVecs v, double* __restrict__ St, double* __restrict__ signal_t, int prescale) {
   const int b = blockIdx.z, tau = blockIdx.y;
   const int j = blockIdx.x * blockDim.x + threadIdx.x;   // output column (0 = constant)
   const int n = nsel[b], t = date_t[b] - tau;
@@ -179,7 +179,7 @@ standardize_kernel(PanelView pv, int NP, int P, long ldP, const int* __restrict_
   }
   const double* __restrict__ vs = pv.vol_scale + (long)t * pv.N;
   const double* __restrict__ slb = v.sl + (long)b * NP;
-  const double* __restrict__ gprev = (tau >= 2 && tau <= pv.lb) ? v.g + ((long)b * nt + (tau - 1)) * NP : nullptr;
+  const double* __restrict__ gprev = (prescale && tau >= 2 && tau <= pv.lb) ? v.g + ((long)b * nt + (tau - 1)) * NP : nullptr;
   double* __restrict__ out = St + (((long)b * nt + tau) * NP) * ldP + j;
   double* __restrict__ sig = (tau == 0 && signal_t) ? signal_t + (long)b * NP * P + j : nullptr;
 #pragma unroll 4
@@ -609,9 +609,9 @@ int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* l
 }
 
 int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
-                const BatchVecs& v, double* St, double* signal_t, cudaStream_t s) {
+                const BatchVecs& v, double* St, double* signal_t, bool prescale, cudaStream_t s) {
   dim3 grid(ceil_div(P, 128), pv.lb + 2, B);
-  standardize_kernel<<<grid, 128, NP * sizeof(int), s>>>(pv, NP, P, ldP, date_t, sel, nsel, v, St, signal_t);
+  standardize_kernel<<<grid, 128, NP * sizeof(int), s>>>(pv, NP, P, ldP, date_t, sel, nsel, v, St, signal_t, prescale ? 1 : 0);
   PFML_CHECK_LAUNCH();
   return 0;
 }

@@ -52,7 +52,8 @@ int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* l
                   double mu, double gam, double* x, double* sgr, double* yv, double* isl, double* sl, cudaStream_t s);
 
 int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
-                const BatchVecs& v, double* St /*[B][lb+2][NP][ldP]*/, double* signal_t /*[B][NP][P] or null*/, cudaStream_t s);
+                const BatchVecs& v, double* St /*[B][lb+2][NP][ldP]*/, double* signal_t /*[B][NP][P] or null*/, bool prescale /* g_{tau-1} row scale for tau in 2..lb */,
+                cudaStream_t s);
 
 // n x n helpers on [B][NP][NP] buffers
 int copy2(int B, long n_elem, const double* src, double* d1, double* d2, cudaStream_t s);

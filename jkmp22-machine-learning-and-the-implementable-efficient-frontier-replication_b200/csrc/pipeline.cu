@@ -259,6 +259,7 @@ struct StepWs {
   double *XC, *XCl1, *Ut, *Ev, *G;
   int8_t *eAs, *eBs; double *esa, *esb; int *eex, *eerr;   // INT8-emulated GEMM operands (emu.cu)
   double* chain;                                            // B~_2 .. B~_{lb-1} of the chain (B~_1 sits in Ya)
+  int8_t* eMs; double* esm;                                 // B-type slices of m~ (kept through the chain / term loop)
   double *St, *Za, *Zb, *Nn, *Nl1, *OM, *BS, *OMC;
   double *risk_tmp, *tc_tmp;
   size_t bytes;
@@ -305,6 +306,7 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.esa = c.take<double>((size_t)B * Pn); w.esb = c.take<double>((size_t)B * Pn);
   w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64);
   w.chain = nt >= 5 ? c.take<double>((size_t)(nt - 4) * BNN) : nullptr;   // lb - 2 matrices
+  w.eMs = c.take<int8_t>(emu_b_slices_bytes(B, NP, NP)); w.esm = c.take<double>((size_t)B * NP);
   w.risk_tmp = need_risk ? c.take<double>((size_t)B * P * P) : nullptr;
   w.tc_tmp = need_tc ? c.take<double>((size_t)B * P * P) : nullptr;
   w.bytes = c.off;
@@ -365,20 +367,89 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     PFML_TRY(mt0_stieltjes(B, NP, pv.K, n_sel, w.v, w.Ut, w.Ev, w.G, w.m.mt, status, s));
     PFML_TRY(fixed_point(B, NP, pv.iterations, w.m, status, s, &mt));
   }
+  const bool emu = use_emu() && emu_shape_ok(NP, P, NP);
+  const bool emu_nn = emu && emu_shape_ok(NP, NP, NP);
+  // direct form of the n x P sums (INT8 path): Z = sum_k B~_k S~_{k+1} term by term next to the chain products
+  const bool direct = emu_nn && lb - 1 <= 16 && w.chain != nullptr;
+  const double* emu_a_cur = nullptr;       // whose slices currently sit in w.eAs
+  if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int), s));
   // ---- a6 standardise (after m~: the signal slabs reuse the quadrature stack's memory) -------------
   {
     ProfScope ps(T_STD, s);
-    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, s));
+    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, !direct, s));
   }
   // free n x n buffers after m_tilde: x, sgr, Mdb, Ya, Yb, Wk, T1 and whichever of {mt, Xinv} is not `mt`
   double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
   double* spare = (mt == w.m.mt) ? w.m.Xinv : w.m.mt;
 
-  const bool emu = use_emu() && emu_shape_ok(NP, P, NP);
-  const bool emu_nn = emu && emu_shape_ok(NP, NP, NP);
-  const double* emu_a_cur = nullptr;       // whose slices currently sit in w.eAs
-  if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int), s));
-
+  // one n x n x P product D = alpha * rs o (A X) + E on whichever tensor pipe is selected; A is sliced on demand
+  auto nxP = [&](const double* A, const double* X, long sX, double alpha, const double* rs, long s_rs, const double* E, long sE,
+                 double* D, long sD) -> int {
+    if (emu) {
+      if (emu_a_cur != A) {
+        PFML_TRY(emu_slice_a(A, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+        emu_a_cur = A;
+      }
+      PFML_TRY(emu_slice_b(X, ldP, sX, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      return emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, alpha, rs, s_rs, E ? 1.0 : 0.0, E, ldP, sE, D, ldP, sD, w.eerr, s);
+    }
+    GemmP g;
+    g.A = A; g.lda = NP; g.sA = NN; g.B = X; g.ldb = ldP; g.sB = sX; g.D = D; g.ldd = ldP; g.sD = sD;
+    g.M = NP; g.N = P; g.K = NP; g.alpha = alpha; g.rs = rs; g.s_rs = s_rs;
+    if (E) { g.E = E; g.lde = ldP; g.sE = sE; g.beta = 1.0; }
+    return gemm(g, B, s);
+  };
+  double* Z = nullptr;
+  if (direct) {
+    // ---- a7 + a8 together: for k = 1 .. lb-1 the slices of B~_k serve two products, the chain step
+    //   B~_{k+1} = B~_k m~ G_{k+1} and the term Z += B~_k S~_{k+1} (Z starts as S~_1).  m~ is sliced once as a B operand.
+    PFML_TRY(chain_init(B, NP, mt, gv(1), sg, Bt_a, CB, s));
+    PFML_TRY(emu_slice_b(mt, NP, NN, NP, NP, B, w.eMs, w.esm, w.eex, w.eerr, s));
+    const double* bk[16];
+    bk[0] = Bt_a;
+    Z = w.Za;
+    for (int k = 1; k < lb; k++) {
+      const bool last = (k == lb - 1);
+      PFML_TRY(emu_slice_a(Bt_a, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+      {
+        ProfScope ps(T_CHAIN, s);
+        EmuExtra x;
+        x.cs = gv(k + 1); x.s_cs = sg;
+        double* out = last ? B11 : w.chain + (size_t)(k - 1) * B * NN;
+        PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eMs, w.esm, NP, NP, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, out, NP, NN, x, w.eerr, s));
+        if (!last) bk[k] = out;
+        Bt_a = out;
+      }
+      {
+        ProfScope ps(T_HORNER, s);
+        PFML_TRY(emu_slice_b(St(k + 1), ldP, sSt, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+        const double* E = (k == 1) ? St(1) : Z;
+        PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, E, ldP, (k == 1) ? sSt : nP, Z, ldP, nP, w.eerr, s));
+      }
+    }
+    // NOTE: in iteration k the A slices are those of B~_k (sliced before the chain step overwrote Bt_a's role)
+    {
+      ProfScope ps(T_CHAIN, s);
+      // const_l1~ = I + sum_k B~_k + B11 -> Wk (to be inverted);  const~ = I + m~ (G_0 CB) -> spare (to be inverted)
+      PFML_TRY(chain_sum(B, NP, lb - 1, bk, B11, gv(0), sg, w.m.Wk, CBs, s));
+      PFML_TRY(emu_slice_a(mt, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+      PFML_TRY(emu_slice_b(CBs, NP, NN, NP, NP, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      EmuExtra x;
+      x.diag = 1.0;
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, NP, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, spare, NP, NN, x, w.eerr, s));
+    }
+    {
+      ProfScope ps(T_HORNER, s);
+      // N = S~_0 + m~ G_0 Z  (the A slices of m~ are still in place);  N_l1 = Z + B11 S~_{lb+1}
+      double* ZG = w.Zb;
+      PFML_TRY(row_scale(B, NP, P, ldP, nP, Z, gv(0), sg, ZG, ldP, nP, s));
+      PFML_TRY(emu_slice_b(ZG, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, St(0), ldP, sSt, w.Nn, ldP, nP, w.eerr, s));
+      PFML_TRY(emu_slice_a(B11, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+      PFML_TRY(emu_slice_b(St(lb + 1), ldP, sSt, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, Z, ldP, nP, w.Nl1, ldP, nP, w.eerr, s));
+    }
+  } else {
   // ---- a7 chain of n x n products (tilde domain) ------------------------------------------------
   //   B~_1 = m~ G_1, B~_{k+1} = B~_k m~ G_{k+1};  CB = sum_{k=0}^{lb-1} B~_k;  B11 = B~_lb
   {
@@ -441,24 +512,6 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   // ---- a8 Horner accumulation of the n x P sums -------------------------------------------------
   //   Z'_j = G_j (S~_{j+1} + m~ Z'_{j+1}),  Z'_{lb-1} = G_{lb-1} S~_lb ;  Z = S~_1 + m~ Z'_1
   //   N = S~_0 + m~ G_0 Z ;  N_l1 = Z + B11 S~_{lb+1}
-  double* Z = nullptr;
-  // one n x n x P product D = alpha * rs o (A X) + E on whichever tensor pipe is selected; A is sliced on demand
-  auto nxP = [&](const double* A, const double* X, long sX, double alpha, const double* rs, long s_rs, const double* E, long sE,
-                 double* D, long sD) -> int {
-    if (emu) {
-      if (emu_a_cur != A) {
-        PFML_TRY(emu_slice_a(A, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
-        emu_a_cur = A;
-      }
-      PFML_TRY(emu_slice_b(X, ldP, sX, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
-      return emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, alpha, rs, s_rs, E ? 1.0 : 0.0, E, ldP, sE, D, ldP, sD, w.eerr, s);
-    }
-    GemmP g;
-    g.A = A; g.lda = NP; g.sA = NN; g.B = X; g.ldb = ldP; g.sB = sX; g.D = D; g.ldd = ldP; g.sD = sD;
-    g.M = NP; g.N = P; g.K = NP; g.alpha = alpha; g.rs = rs; g.s_rs = s_rs;
-    if (E) { g.E = E; g.lde = ldP; g.sE = sE; g.beta = 1.0; }
-    return gemm(g, B, s);
-  };
   {
     ProfScope ps(T_HORNER, s);
     const double* Zp = St(lb);         // already scaled by g_{lb-1} in the standardise kernel
@@ -475,6 +528,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     PFML_TRY(nxP(mt, ZG, nP, 1.0, nullptr, 0, St(0), sSt, w.Nn, nP));
     PFML_TRY(nxP(B11, St(lb + 1), sSt, 1.0, nullptr, 0, Z, nP, w.Nl1, nP));
   }
+  }   // !direct
 
   // ---- a8 solves: omega~ = const~^-1 N, omega~_l1 = const~_l1^-1 N_l1, omega~_chg -----------------
   {
