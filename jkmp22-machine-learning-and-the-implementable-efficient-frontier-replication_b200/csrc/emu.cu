@@ -18,7 +18,7 @@
 // field, fused row / column scale, addend, identity, second output; stores transposed through shared memory).
 #include <cstdlib>
 
-#include "common.cuh"
+#include "kernels.cuh"
 
 namespace pfml {
 
@@ -43,7 +43,10 @@ __host__ __device__ inline int canon(int r, int kk) { return (r % 8) * 16 + (r /
 // (i + j >= ES) have no systematic sign.  Zeros, denormals and values below 2^(e - 8 ES + 1) give all-zero slices.
 __device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* dst, long slice_stride, int8_t* dst2 = nullptr,
                                         long slice_stride2 = 0) {
-  long long f[16];
+  // With the bias Bz = sum_t 0x80 256^t: the bytes g_t of F + Bz satisfy F = sum_t (g_t - 128) 256^t, and g_t - 128 as an
+  // int8 is g_t ^ 0x80 -- all ES balanced digits of an element come from one 64-bit add and one xor.
+  constexpr unsigned long long Bz = 0x8080808080808080ull >> (8 * (8 - ES));
+  unsigned lo[16], hi[16];
 #pragma unroll
   for (int k = 0; k < 16; k++) {
     const long long bits = __double_as_longlong(x[k]);
@@ -51,27 +54,25 @@ __device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* ds
     const unsigned long long mant = ((unsigned long long)bits & 0xFFFFFFFFFFFFFull) | (ex ? (1ull << 52) : 0ull);
     const int sh = 1075 + e - (8 * ES - 2) - ex;           // |F| = round(mant 2^-sh)
     const unsigned long long fv = (ex == 0 || sh >= 64) ? 0ull : (sh > 0 ? ((mant + (1ull << (sh - 1))) >> sh) : (mant << (-sh)));
-    f[k] = bits < 0 ? -(long long)fv : (long long)fv;
+    const unsigned long long g = ((unsigned long long)(bits < 0 ? -(long long)fv : (long long)fv) + Bz) ^ Bz;
+    lo[k] = (unsigned)g; hi[k] = (unsigned)(g >> 32);
   }
-  union U { int8_t b[16]; int4 v; };
-  U u[ES];
 #pragma unroll
-  for (int t = ES - 1; t >= 0; t--) {
+  for (int t = 0; t < ES; t++) {
+    const int p = ES - 1 - t;                              // byte position of digit t (most significant first)
+    int4 v;
+    unsigned w[4];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-      const int8_t d = (int8_t)(f[k] & 0xff);
-      u[t].b[k] = d;
-      f[k] = (f[k] - (long long)d) >> 8;
+    for (int q = 0; q < 4; q++) {
+      const unsigned a0 = p < 4 ? lo[4 * q] : hi[4 * q], a1 = p < 4 ? lo[4 * q + 1] : hi[4 * q + 1];
+      const unsigned a2 = p < 4 ? lo[4 * q + 2] : hi[4 * q + 2], a3 = p < 4 ? lo[4 * q + 3] : hi[4 * q + 3];
+      const unsigned sel = (unsigned)(p & 3) | ((unsigned)((p & 3) + 4) << 4);      // byte p of a, byte p of b
+      const unsigned x01 = __byte_perm(a0, a1, sel), x23 = __byte_perm(a2, a3, sel);
+      w[q] = __byte_perm(x01, x23, 0x5410);
     }
-  }
-#pragma unroll
-  if (dst) {
-#pragma unroll
-    for (int t = 0; t < ES; t++) *reinterpret_cast<int4*>(dst + t * slice_stride) = u[t].v;
-  }
-  if (dst2) {
-#pragma unroll
-    for (int t = 0; t < ES; t++) *reinterpret_cast<int4*>(dst2 + t * slice_stride2) = u[t].v;
+    v.x = (int)w[0]; v.y = (int)w[1]; v.z = (int)w[2]; v.w = (int)w[3];
+    if (dst) *reinterpret_cast<int4*>(dst + t * slice_stride) = v;
+    if (dst2) *reinterpret_cast<int4*>(dst2 + t * slice_stride2) = v;
   }
 }
 
@@ -210,6 +211,198 @@ slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, in
     for (int j = 0; j < 16; j++) y[j] = x[h * 16 + j];
     const int kk = (kq & 1) * 32 + h * 16;
     slice16(y, e, base ? base + canon(nn, kk) : nullptr, (long)EBN * EKC, baseA ? baseA + canon(n % EBM, kk) : nullptr, (long)EBM * EKC);
+  }
+}
+
+// Standardise + scale (the arithmetic of standardize_kernel in kernels.cu, PFML_Input_Data.py:357-388) for the slabs that
+// are only ever B operands of the INT8 products: the standardised, tilde-scaled column goes straight into its
+// base-256 digits in the B-type layout, no FP64 copy is written.  A CTA owns 64 output columns (one B-type block);
+// thread = (column, row quarter): it owns the 16-row groups ib = rq, rq + 4, ... in all three passes (mean; centred sum
+// of squares + largest scaled deviation; digits), partial sums meet in shared memory in a fixed order.
+constexpr int SSQ = 4;   // row quarters
+__global__ void __launch_bounds__(64 * SSQ)
+standardize_slice_kernel(PanelView pv, int NP, int P, int tau0, const int* __restrict__ date_t, const int* __restrict__ sel,
+                         const int* __restrict__ nsel, BatchVecs v, int8_t* __restrict__ out, long slab_bytes,
+                         double* __restrict__ scale_out, int* __restrict__ err) {
+  const int b = blockIdx.z, tau = tau0 + blockIdx.y;
+  const int cj = threadIdx.x & 63, rq = threadIdx.x >> 6;
+  const int j = blockIdx.x * EBN + cj;                   // output column (0 = constant)
+  const int n = nsel[b], t = date_t[b] - tau;
+  const int CB = (P + EBN - 1) / EBN, KB = NP / EKC, NG = NP / 16;
+  // per-row factors once per CTA: gather index, 1 / vol_scale and sqrt(lambda)
+  extern __shared__ double s_dyn[];
+  double* s_inv = s_dyn;
+  double* s_sl = s_dyn + NP;
+  double* s_red = s_dyn + 2 * NP;                        // [SSQ][64]
+  int* s_sel = reinterpret_cast<int*>(s_dyn + 2 * NP + SSQ * 64);
+  const double* __restrict__ vs = pv.vol_scale + (long)t * pv.N;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int si = sel[(long)b * NP + i];
+    s_sel[i] = si;
+    s_inv[i] = 1.0 / vs[si];
+    s_sl[i] = v.sl[(long)b * NP + i];
+  }
+  __syncthreads();
+  const bool real = j < P;
+  const double* __restrict__ X = pv.rff + (long)t * pv.N * pv.p + (j > 0 ? j - 1 : 0);
+  double mean = 0.0, scale = 0.0, mx = 0.0;
+  bool bad = false;
+  // pass 1: mean
+  double part = 0.0;
+  if (real && j > 0)
+    for (int ib = rq; ib < NG; ib += SSQ) {
+      const int i1 = min(ib * 16 + 16, n);
+      for (int i = ib * 16; i < i1; i++) part += X[(long)s_sel[i] * pv.p];
+    }
+  s_red[rq * 64 + cj] = part;
+  __syncthreads();
+  if (real && j > 0) {
+    double sum = 0.0;
+#pragma unroll
+    for (int q = 0; q < SSQ; q++) sum += s_red[q * 64 + cj];
+    mean = sum / (double)n;
+  }
+  __syncthreads();
+  // pass 2: centred sum of squares and the largest |sqrt(lambda) / vol_scale * c|
+  part = 0.0;
+  if (real)
+    for (int ib = rq; ib < NG; ib += SSQ) {
+      const int i1 = min(ib * 16 + 16, n);
+      for (int i = ib * 16; i < i1; i++) {
+        const double c = (j == 0) ? 1.0 : X[(long)s_sel[i] * pv.p] - mean;
+        part += c * c;
+        const double a = fabs(s_sl[i] * (s_inv[i] * c));
+        bad |= !(a <= 1.7976931348623157e308);
+        mx = fmax(mx, a);
+      }
+    }
+  s_red[rq * 64 + cj] = part;
+  __syncthreads();
+  double ss = 0.0;
+#pragma unroll
+  for (int q = 0; q < SSQ; q++) ss += s_red[q * 64 + cj];
+  __syncthreads();
+  s_red[rq * 64 + cj] = mx;
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < SSQ; q++) mx = fmax(mx, s_red[q * 64 + cj]);
+  if (real) {
+    scale = (j == 0) ? sqrt(1.0 / (double)n) : sqrt(1.0 / ss);   // constant: not de-meaned, sum of squares = n
+    mx *= scale;                                                  // largest |value| up to rounding (digits tolerate 1.98 * 2^e)
+    bad |= !(mx <= 1.7976931348623157e308);
+  }
+  if (bad) atomicOr(err, 16);                               // NaN / Inf cannot be sliced: reported through the status array
+  const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
+  if (real && rq == 0) scale_out[((long)blockIdx.y * gridDim.z + b) * P + j] = scalbn(kBScale, e);
+  // pass 3: digits
+  int8_t* base = out + (long)blockIdx.y * slab_bytes + (((long)b * CB + blockIdx.x) * KB) * (long)EB_STAGE;
+  for (int ib = rq; ib < NG; ib += SSQ) {
+    const int i0 = ib * 16;
+    double x[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      const int i = i0 + k;
+      double tv = 0.0;
+      if (real && i < n) {
+        const double c = (j == 0) ? 1.0 : X[(long)s_sel[i] * pv.p] - mean;
+        tv = s_sl[i] * (s_inv[i] * (c * scale));
+      }
+      x[k] = tv;
+    }
+    slice16(x, e, base + (long)(i0 / EKC) * EB_STAGE + canon(cj, i0 % EKC), (long)EBN * EKC);
+  }
+}
+
+// The same for NP <= 512 in ONE pass over the gathered panel rows: a CTA owns 32 output columns, thread = (column,
+// group of 32 rows) keeps its values in registers from the statistics to the digits (like slice_nmajor512_kernel).
+__global__ void __launch_bounds__(512, 1)
+standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __restrict__ date_t, const int* __restrict__ sel,
+                            const int* __restrict__ nsel, BatchVecs v, int8_t* __restrict__ out, long slab_bytes,
+                            double* __restrict__ scale_out, int* __restrict__ err) {
+  // blockIdx.z walks the diagonals b - tau = const: with consecutive month-ends the (date, lag) pairs of one diagonal
+  // read the same panel month, so launching them together keeps that month in L2 (DRAM reads 4.9 GB -> ~1 GB)
+  const int ntau = gridDim.y, nB = gridDim.z - ntau + 1;
+  const int b = (int)blockIdx.z + (int)blockIdx.y - (ntau - 1), tau = tau0 + blockIdx.y;
+  if (b < 0 || b >= nB) return;
+  const int lane = threadIdx.x & 31, rg = threadIdx.x >> 5;      // rows rg * 32 .. rg * 32 + 31
+  const int j = blockIdx.x * 32 + lane;                           // output column (0 = constant)
+  const int n = nsel[b], t = date_t[b] - tau;
+  const int CB = (P + EBN - 1) / EBN, KB = NP / EKC;
+  // row factor sqrt(lambda_i) / vol_scale_i once per CTA (the FP64 kernel applies the two factors one after the other:
+  // one rounding more, far below the digit resolution); non-finite factors are caught here, non-finite signals by the
+  // sum of squares below
+  __shared__ double s_rf[512], s_red[16][33];
+  __shared__ int s_sel[512];
+  const double* __restrict__ vs = pv.vol_scale + (long)t * pv.N;
+  bool bad = false;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int si = sel[(long)b * NP + i];
+    s_sel[i] = si;
+    const double rf = v.sl[(long)b * NP + i] * (1.0 / vs[si]);
+    s_rf[i] = rf;
+    bad |= !(fabs(rf) <= 1.7976931348623157e308);
+  }
+  __syncthreads();
+  const bool real = j < P;
+  const double* __restrict__ X = pv.rff + (long)t * pv.N * pv.p + (j > 0 ? j - 1 : 0);
+  const int i0 = rg * 32;
+  double x[32];
+#pragma unroll
+  for (int k = 0; k < 32; k++) {
+    const int i = i0 + k;
+    x[k] = (real && i < n) ? (j == 0 ? 1.0 : X[(long)s_sel[i] * pv.p]) : 0.0;
+  }
+  // mean (the constant column is not de-meaned)
+  double part = 0.0;
+#pragma unroll
+  for (int k = 0; k < 32; k++) part += x[k];
+  s_red[rg][lane] = part;
+  __syncthreads();
+  double mean = 0.0;
+  if (j > 0) {
+#pragma unroll
+    for (int q = 0; q < 16; q++) mean += s_red[q][lane];
+    mean = mean / (double)n;
+  }
+  __syncthreads();
+  // centred values, sum of squares, largest |sqrt(lambda) / vol_scale * c|
+  double mx = 0.0;
+  part = 0.0;
+#pragma unroll
+  for (int k = 0; k < 32; k++) {
+    const int i = i0 + k;
+    const double c = (real && i < n) ? x[k] - mean : 0.0;
+    part += c * c;
+    const double y = (i < n ? s_rf[i] : 0.0) * c;          // scaled below by the column's 1 / norm
+    x[k] = y;
+    mx = fmax(mx, fabs(y));
+  }
+  s_red[rg][lane] = part;
+  __syncthreads();
+  double ss = 0.0;
+#pragma unroll
+  for (int q = 0; q < 16; q++) ss += s_red[q][lane];
+  __syncthreads();
+  s_red[rg][lane] = mx;
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < 16; q++) mx = fmax(mx, s_red[q][lane]);
+  const double scale = real ? ((j == 0) ? sqrt(1.0 / (double)n) : sqrt(1.0 / ss)) : 0.0;
+  mx *= scale;                                               // largest |value| up to rounding (digits tolerate 1.98 * 2^e)
+  bad |= real && !(ss <= 1.7976931348623157e308 && mx <= 1.7976931348623157e308);
+  if (bad) atomicOr(err, 16);
+  const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
+  if (real && rg == 0) scale_out[((long)blockIdx.y * nB + b) * P + j] = scalbn(kBScale, e);
+  if (i0 >= NP || j / EBN >= CB) return;
+  int8_t* base = out + (long)blockIdx.y * slab_bytes + (((long)b * CB + j / EBN) * KB + i0 / EKC) * (long)EB_STAGE;
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    double y[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      y[k] = x[h * 16 + k] * scale;
+    }
+    slice16(y, e, base + canon(j % EBN, (i0 + h * 16) % EKC), (long)EBN * EKC);
   }
 }
 
@@ -529,6 +722,31 @@ int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int
   const int CB = ceil_div(C, EBN), RBA = ceil_div(C, EBM);
   const int blocks = outA ? 4 * RBA : 2 * CB;          // 32 columns per CTA; the padded tail of the last block is zero-filled
   slice_nmajor512_kernel<<<dim3(blocks, batch), 512, 0, s>>>(X, ld, sX, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+// slabs tau0 .. tau0 + ntau - 1 of the standardised signals as B-type slices (out: ntau blocks of emu_b_slices_bytes(B, NP, P),
+// scale_out [ntau][B][P])
+int emu_standardize_slices(const PanelView& pv, int B, int NP, int P, int tau0, int ntau, const int* date_t, const int* sel,
+                           const int* nsel, const BatchVecs& v, int8_t* out, double* scale_out, int* err, cudaStream_t s) {
+  const int CB = ceil_div(P, EBN);
+  dim3 grid(CB, ntau, B);
+  if (NP <= 512) {
+    standardize_slice512_kernel<<<dim3(2 * CB, ntau, B + ntau - 1), 512, 0, s>>>(pv, NP, P, tau0, date_t, sel, nsel, v, out,
+                                                                      (long)emu_b_slices_bytes(B, NP, P), scale_out, err);
+    PFML_CHECK_LAUNCH();
+    return 0;
+  }
+  const size_t smem = (size_t)NP * (2 * sizeof(double) + sizeof(int)) + SSQ * 64 * sizeof(double);
+  if (smem > 200 * 1024) {
+    set_error("emu_standardize_slices: universe of %d stocks needs %zu bytes of shared memory", NP, smem);
+    return -2;
+  }
+  if (smem > 48 * 1024)
+    PFML_CUDA_OK(cudaFuncSetAttribute(standardize_slice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  standardize_slice_kernel<<<grid, 64 * SSQ, smem, s>>>(pv, NP, P, tau0, date_t, sel, nsel, v, out,
+                                                        (long)emu_b_slices_bytes(B, NP, P), scale_out, err);
   PFML_CHECK_LAUNCH();
   return 0;
 }

@@ -609,8 +609,8 @@ int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* l
 }
 
 int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
-                const BatchVecs& v, double* St, double* signal_t, bool prescale, cudaStream_t s) {
-  dim3 grid(ceil_div(P, 128), pv.lb + 2, B);
+                const BatchVecs& v, double* St, double* signal_t, bool prescale, int ntau, cudaStream_t s) {
+  dim3 grid(ceil_div(P, 128), ntau, B);
   standardize_kernel<<<grid, 128, NP * sizeof(int), s>>>(pv, NP, P, ldP, date_t, sel, nsel, v, St, signal_t, prescale ? 1 : 0);
   PFML_CHECK_LAUNCH();
   return 0;

@@ -53,7 +53,7 @@ int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* l
 
 int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
                 const BatchVecs& v, double* St /*[B][lb+2][NP][ldP]*/, double* signal_t /*[B][NP][P] or null*/, bool prescale /* g_{tau-1} row scale for tau in 2..lb */,
-                cudaStream_t s);
+                int ntau /* slabs 0 .. ntau-1 are written */, cudaStream_t s);
 
 // n x n helpers on [B][NP][NP] buffers
 int copy2(int B, long n_elem, const double* src, double* d1, double* d2, cudaStream_t s);
@@ -62,6 +62,8 @@ int db_update_M(int B, int NP, double* M, const double* Mi, double* Wk, const do
 int mt0_from_sqrt(int B, int NP, const double* x, const double* Y, double* mt, cudaStream_t s);
 int fp_build(int B, int NP, const double* x, const double* yv, const double* mt, const double* sgr, double* Wk, cudaStream_t s);
 int chain_init(int B, int NP, const double* mt, const double* g1, long sg, double* Bt, double* CB, cudaStream_t s);
+int emu_standardize_slices(const PanelView& pv, int B, int NP, int P, int tau0, int ntau, const int* date_t, const int* sel,
+                           const int* nsel, const BatchVecs& v, int8_t* out, double* scale_out, int* err, cudaStream_t s);
 int add_mat(int B, long n_elem, const double* a, const double* b, double* out, cudaStream_t s);
 int sym_finish(int B, int P, double* risk, double* tc, double* denom, cudaStream_t s);
 int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11, const double* g0, long sg, double* wk, double* cbs,

@@ -260,6 +260,7 @@ struct StepWs {
   int8_t *eAs, *eBs; double *esa, *esb; int *eex, *eerr;   // INT8-emulated GEMM operands (emu.cu)
   double* chain;                                            // B~_2 .. B~_{lb-1} of the chain (B~_1 sits in Ya)
   int8_t* eMs; double* esm;                                 // B-type slices of m~ (kept through the chain / term loop)
+  int8_t* eSs; double* eSsb;                                // B-type slices of the signal slabs 2 .. lb+1 and their scales
   double *St, *Za, *Zb, *Nn, *Nl1, *OM, *BS, *OMC;
   double *risk_tmp, *tc_tmp;
   size_t bytes;
@@ -307,6 +308,8 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64);
   w.chain = nt >= 5 ? c.take<double>((size_t)(nt - 4) * BNN) : nullptr;   // lb - 2 matrices
   w.eMs = c.take<int8_t>(emu_b_slices_bytes(B, NP, NP)); w.esm = c.take<double>((size_t)B * NP);
+  w.eSs = nt >= 3 ? c.take<int8_t>((size_t)(nt - 2) * emu_b_slices_bytes(B, NP, P)) : nullptr;
+  w.eSsb = nt >= 3 ? c.take<double>((size_t)(nt - 2) * B * P) : nullptr;
   w.risk_tmp = need_risk ? c.take<double>((size_t)B * P * P) : nullptr;
   w.tc_tmp = need_tc ? c.take<double>((size_t)B * P * P) : nullptr;
   w.bytes = c.off;
@@ -376,7 +379,9 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   // ---- a6 standardise (after m~: the signal slabs reuse the quadrature stack's memory) -------------
   {
     ProfScope ps(T_STD, s);
-    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, !direct, s));
+    // direct form: only S~_0 and S~_1 are needed in FP64 (addends); the other slabs go straight to INT8 digits
+    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, !direct, direct ? 2 : nt, s));
+    if (direct) PFML_TRY(emu_standardize_slices(pv, B, NP, P, 2, lb, date_t, sel, n_sel, w.v, w.eSs, w.eSsb, w.eerr, s));
   }
   // free n x n buffers after m_tilde: x, sgr, Mdb, Ya, Yb, Wk, T1 and whichever of {mt, Xinv} is not `mt`
   double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
@@ -400,6 +405,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     return gemm(g, B, s);
   };
   double* Z = nullptr;
+  const size_t slabS = emu_b_slices_bytes(B, NP, P);
   if (direct) {
     // ---- a7 + a8 together: for k = 1 .. lb-1 the slices of B~_k serve two products, the chain step
     //   B~_{k+1} = B~_k m~ G_{k+1} and the term Z += B~_k S~_{k+1} (Z starts as S~_1).  m~ is sliced once as a B operand.
@@ -422,9 +428,9 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       }
       {
         ProfScope ps(T_HORNER, s);
-        PFML_TRY(emu_slice_b(St(k + 1), ldP, sSt, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
-        const double* E = (k == 1) ? St(1) : Z;
-        PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, E, ldP, (k == 1) ? sSt : nP, Z, ldP, nP, w.eerr, s));
+        const double* E = (k == 1) ? St(1) : Z;     // slab k + 1 was sliced by the standardise kernel
+        PFML_TRY(emu_mma(w.eAs, w.esa, w.eSs + (size_t)(k - 1) * slabS, w.eSsb + (size_t)(k - 1) * B * P, NP, P, NP, B, 1.0, nullptr, 0,
+                         1.0, E, ldP, (k == 1) ? sSt : nP, Z, ldP, nP, w.eerr, s));
       }
     }
     // NOTE: in iteration k the A slices are those of B~_k (sliced before the chain step overwrote Bt_a's role)
@@ -446,8 +452,8 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       PFML_TRY(emu_slice_b(ZG, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
       PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, St(0), ldP, sSt, w.Nn, ldP, nP, w.eerr, s));
       PFML_TRY(emu_slice_a(B11, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
-      PFML_TRY(emu_slice_b(St(lb + 1), ldP, sSt, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
-      PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, Z, ldP, nP, w.Nl1, ldP, nP, w.eerr, s));
+      PFML_TRY(emu_mma(w.eAs, w.esa, w.eSs + (size_t)(lb - 1) * slabS, w.eSsb + (size_t)(lb - 1) * B * P, NP, P, NP, B, 1.0, nullptr, 0,
+                       1.0, Z, ldP, nP, w.Nl1, ldP, nP, w.eerr, s));
     }
   } else {
   // ---- a7 chain of n x n products (tilde domain) ------------------------------------------------
