@@ -66,7 +66,9 @@ int pfml_growth_ratio(const double* tr_ld0, const double* mu_ld0, long n, double
  * universe, n_sel [B] their count, NP = pfml_padded_n(n_max).  Outputs are in feat_all order
  * (constant, cos 1..p/2, sin 1..p/2; PFML_Input_Data.py:221,:484,:489), P = p + 1:
  *   r_tilde [B][P], denom/risk/tc [B][P][P], signal_t [B][NP][P] (rows >= n_sel[b] are zero).
- * risk, tc, signal_t may be NULL.  status [B] int32 (may be NULL) receives numerical-failure bits. */
+ * risk, tc, signal_t may be NULL.  status [B] int32 (may be NULL) receives numerical-failure bits.
+ * The n x n and n x P products run as FP64-equivalent GEMMs on the INT8 tensor cores (see pfml_dgemm_emulated;
+ * pfml_set_emulation(0) or PFML_EMULATE_FP64=0 selects the FP64 DMMA kernel for them). */
 int pfml_padded_n(int n_max);
 size_t pfml_date_steps_workspace_bytes(const pfml_panel_t* panel, int B, int n_max);
 int pfml_date_steps(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
