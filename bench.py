@@ -319,7 +319,12 @@ def run_ours(args, rank, world, local_rank):
     names = [lib.pfml_prof_tag_name(i).decode() for i in range(nt)]
 
     # ---- e2e: host buffers in / out through pfml_date_steps_host ------------------------------------
+    # pinned host buffers are placed on the NUMA node of the allocating thread: bind it to the GPU's node while they are
+    # allocated (with 8 ranks the downloads otherwise cross the socket link), then give the affinity back
+    numa = bind_to_gpu_numa(torch, dev)
     blk = host_mod.HostBlock(panel, months, pin=True)
+    if numa is not None:
+        os.sched_setaffinity(0, numa["before"])
     for _ in range(max(1, min(args.warmup, 2))):
         blk.run(chunk=args.chunk, device=local_rank)
     barrier()
@@ -390,7 +395,8 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clocks,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(blk.h2d_bytes), "d2h_bytes_per_step": int(blk.d2h_bytes),
                 "outputs": "r_tilde, denom, risk, tc, signal_t (everything PFML_Input_Data.py stores per date)",
-                "chunk": args.chunk, "max_abs_diff_vs_resident_path": chk},
+                "chunk": args.chunk, "max_abs_diff_vs_resident_path": chk,
+                "host_buffers": "pinned, allocated on the GPU's NUMA node" if numa else "pinned"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor",
                      "kernel": "pfml::emu_gemm_kernel (tcgen05.mma kind::i8, TMEM accumulators, bulk-TMA operands): FP64-equivalent "
@@ -414,6 +420,22 @@ def run_ours(args, rank, world, local_rank):
                          "sample": f"{cpu_n} date-steps of the same N=500, p=1024 workload in {cpu_dt:.1f} s (numpy oracle, all host BLAS threads)"},
     }
     print(json.dumps(out))
+
+
+def bind_to_gpu_numa(torch, dev):
+    """Set this thread's CPU affinity to the cores NVML reports as local to `dev`; returns the previous affinity."""
+    try:
+        import pynvml
+        before = os.sched_getaffinity(0)
+        pr = torch.cuda.get_device_properties(dev)
+        bus_id = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus_id.encode())
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        after = os.sched_getaffinity(0)
+        return {"before": before, "cores": len(after)}
+    except Exception:
+        return None
 
 
 def main():
