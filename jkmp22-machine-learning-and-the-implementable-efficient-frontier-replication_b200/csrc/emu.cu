@@ -519,7 +519,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: 36 slice pairs x 2 k-steps per stage, accumulator d = i + j at TMEM column d * 64 =====
+    // ===== MMA issuer: ES (ES + 1) / 2 digit pairs x 2 k-slabs per stage, accumulator d = i + j at TMEM column d * 64 =====
     const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(EBN >> 3) << 17) | ((uint32_t)(EBM >> 4) << 24);
     long it = 0;
     int tl = 0;
@@ -786,8 +786,7 @@ int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const doubl
     cfg[dev & 63] = true;
   }
   const long tiles = (long)batch * p.MB * p.NB;
-  static const int mult = getenv("PFML_EMU_GRID") ? atoi(getenv("PFML_EMU_GRID")) : 1;   // tuning aid: CTAs per SM (0 = one per tile)
-  const long want = mult > 0 ? (long)mult * n_sm[dev & 63] : tiles;
+  const long want = n_sm[dev & 63];                       // persistent: one CTA per SM (it owns the SM's whole TMEM)
   const int grid = (int)(tiles < want ? tiles : want);
   prof_begin(-2, s);
   emu_gemm_kernel<<<grid, EMU_THREADS, smem, s>>>(p);
