@@ -174,7 +174,7 @@ slice_nmajor_kernel(const double* __restrict__ X, long ld, long sX, int K, int C
 __global__ void __launch_bounds__(512, 1)
 slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, int CB, int* __restrict__ ex, double* __restrict__ scale,
                        double extra, int8_t* __restrict__ out, int RBA, double* __restrict__ scaleA, int8_t* __restrict__ outA,
-                       int* __restrict__ err) {
+                       int* __restrict__ err, const double* __restrict__ rsc, long s_rsc) {
   constexpr int K = 512, KB = K / EKC;
   __shared__ double red[16][33];
   const int z = blockIdx.y, lane = threadIdx.x & 31, kq = threadIdx.x >> 5;
@@ -186,6 +186,11 @@ slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, in
     const double* b = X + (long)z * sX + (long)(kq * 32) * ld + n;
 #pragma unroll
     for (int j = 0; j < 32; j++) x[j] = b[(long)j * ld];
+    if (rsc) {                                             // optional row scale (the k index of the product) fused into the slicing
+      const double* r = rsc + (long)z * s_rsc + kq * 32;
+#pragma unroll
+      for (int j = 0; j < 32; j++) x[j] *= r[j];
+    }
 #pragma unroll
     for (int j = 0; j < 32; j++) { const double v = fabs(x[j]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
   } else {
@@ -705,7 +710,7 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
   if (K == 512) {
     // 64-column blocks are written by two CTAs of 32 columns; the padded half of the last block must be zero-filled too
     slice_nmajor512_kernel<<<dim3(2 * ceil_div(N, EBN), batch), 512, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, kBScale,
-                                                                             out, 0, nullptr, nullptr, err);
+                                                                             out, 0, nullptr, nullptr, err, nullptr, 0);
     PFML_CHECK_LAUNCH();
     return 0;
   }
@@ -718,10 +723,10 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
 
 // X [512][C] (C contiguous) -> B-type slices of X (outB, may be null) and / or A-type slices of X' (outA, may be null)
 int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
-                        double* sa, int* err, cudaStream_t s) {
+                        double* sa, int* err, cudaStream_t s, const double* row_scale, long s_row_scale) {
   const int CB = ceil_div(C, EBN), RBA = ceil_div(C, EBM);
   const int blocks = outA ? 4 * RBA : 2 * CB;          // 32 columns per CTA; the padded tail of the last block is zero-filled
-  slice_nmajor512_kernel<<<dim3(blocks, batch), 512, 0, s>>>(X, ld, sX, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err);
+  slice_nmajor512_kernel<<<dim3(blocks, batch), 512, 0, s>>>(X, ld, sX, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err, row_scale, s_row_scale);
   PFML_CHECK_LAUNCH();
   return 0;
 }

@@ -447,9 +447,13 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     {
       ProfScope ps(T_HORNER, s);
       // N = S~_0 + m~ G_0 Z  (the A slices of m~ are still in place);  N_l1 = Z + B11 S~_{lb+1}
-      double* ZG = w.Zb;
-      PFML_TRY(row_scale(B, NP, P, ldP, nP, Z, gv(0), sg, ZG, ldP, nP, s));
-      PFML_TRY(emu_slice_b(ZG, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      if (NP == 512) {                  // G_0 Z is only ever this product's B operand: the row scale rides in the slicing
+        PFML_TRY(emu_slice_nmajor512(Z, ldP, nP, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s, gv(0), sg));
+      } else {
+        double* ZG = w.Zb;
+        PFML_TRY(row_scale(B, NP, P, ldP, nP, Z, gv(0), sg, ZG, ldP, nP, s));
+        PFML_TRY(emu_slice_b(ZG, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      }
       PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, St(0), ldP, sSt, w.Nn, ldP, nP, w.eerr, s));
       PFML_TRY(emu_slice_a(B11, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
       PFML_TRY(emu_mma(w.eAs, w.esa, w.eSs + (size_t)(lb - 1) * slabS, w.eSsb + (size_t)(lb - 1) * B * P, NP, P, NP, B, 1.0, nullptr, 0,
