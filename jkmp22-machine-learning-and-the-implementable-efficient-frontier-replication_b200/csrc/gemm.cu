@@ -297,7 +297,10 @@ int gemm(const GemmP& p, int batch, cudaStream_t stream) {
   // Measured on B200 for the Horner step (148 x [512 x 1025 x 512]): 30.5 TFLOP/s, against 24.2 for
   // 128x128 / 8 warps / 1 CTA per SM and 27.9 for 128x64 / 2 CTAs per SM -- independent CTAs hide each other's
   // per-k-tile barrier, which a single big CTA cannot (profiles/r01_gemm_tile_sweep.md).
-  rc = dispatch_layout<64, 64, 32, 32, 16, 3, 3>(p, batch, stream, vec);
+  // Small outputs (the 128- and 256-blocks of the inverse recursion): 4 CTAs per SM, so that batch x 4 or batch x 16
+  // tiles of a 148-matrix batch fill whole waves (592 resident CTAs) instead of 1.33 / 5.33 waves of 444.
+  if (p.M <= 256 && p.N <= 256) rc = dispatch_layout<64, 64, 32, 32, 16, 3, 4>(p, batch, stream, vec);
+  else rc = dispatch_layout<64, 64, 32, 32, 16, 3, 3>(p, batch, stream, vec);
   prof_end(-1, stream, gemm_flops(p, batch), 0.0);
   return rc;
 }
