@@ -105,38 +105,45 @@ __global__ void slice_kmajor_kernel(const double* __restrict__ X, long ld, long 
   }
 }
 
-// The same for K == 512 in one pass over the data: a warp per row, every lane keeps its 16 consecutive values in
-// registers between the row maximum and the slicing.
+// The same for K == 512 in one pass over the data.  A CTA owns 8 rows: warp w takes the 64-byte k chunk w of all of
+// them, lane = (row r, 16-element group c), so that one store instruction of a warp writes four whole 8 x 16 B core
+// matrices (512 contiguous bytes) of the operand layout; the row maxima meet in shared memory.
 template <int BR>
 __global__ void __launch_bounds__(256)
 slice_kmajor512_kernel(const double* __restrict__ X, long ld, long sX, int R, int8_t* __restrict__ out,
                        double* __restrict__ scale, double extra, int* __restrict__ err) {
   constexpr int K = 512, KB = K / EKC;
-  const int z = blockIdx.y, row = blockIdx.x * 8 + threadIdx.x / 32, lane = threadIdx.x & 31;
+  static_assert(EKC == 64, "one warp per 64-byte k chunk");
+  __shared__ double s_mx[8][8];
+  const int z = blockIdx.y, w = threadIdx.x >> 5, lane = threadIdx.x & 31, r = lane & 7, c = lane >> 3;
+  const int row = blockIdx.x * 8 + r;
   const int RB = (R + BR - 1) / BR;
-  if (row >= RB * BR) return;
   constexpr long STAGE = (long)ES * BR * EKC;
-  int8_t* base = out + (((long)z * RB + row / BR) * KB) * STAGE;
   double x[16];
-  int e = 0;
+  double mx = 0.0;
+  bool bad = false;
   if (row < R) {
-    const double2* a = reinterpret_cast<const double2*>(X + (long)z * sX + (long)row * ld + lane * 16);
-    double mx = 0.0;
-    bool bad = false;
+    const double2* a = reinterpret_cast<const double2*>(X + (long)z * sX + (long)row * ld + w * EKC + c * 16);
 #pragma unroll
     for (int k = 0; k < 8; k++) { const double2 v = a[k]; x[2 * k] = v.x; x[2 * k + 1] = v.y; }
 #pragma unroll
     for (int k = 0; k < 16; k++) { const double v = fabs(x[k]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
-    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (bad) atomicOr(err, 16);
-    e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
-    if (lane == 0) scale[(long)z * R + row] = scalbn(extra, e);
   } else {
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = 0.0;
   }
-  const int k0 = lane * 16;
-  slice16(x, e, base + (long)(k0 / EKC) * STAGE + canon(row % BR, k0 % EKC), (long)BR * EKC);
+  if (bad) atomicOr(err, 16);
+  mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+  mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+  if (c == 0) s_mx[w][r] = mx;
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < 8; q++) mx = fmax(mx, s_mx[q][r]);
+  const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
+  if (w == 0 && c == 0 && row < R) scale[(long)z * R + row] = scalbn(extra, e);
+  if (row >= RB * BR) return;
+  int8_t* base = out + (((long)z * RB + row / BR) * KB + w) * STAGE;
+  slice16(x, e, base + canon(row % BR, c * 16), (long)BR * EKC);
 }
 
 // B-type operand: X [K][C] with C contiguous (ld), scaled per column, blocks of 64 columns.
