@@ -178,14 +178,15 @@ slice_nmajor_kernel(const double* __restrict__ X, long ld, long sX, int K, int C
 // N-major operand X [512][C] in one pass: a CTA owns 32 columns x all 512 k (thread = column, 32 consecutive k held in
 // registers), the column maxima go through shared memory, no separate exponent kernel.  Writes the B-type slices
 // (64-column blocks, `out`) and / or the A-type slices of X' (128-row blocks, `outA`: X' as the left operand).
-__global__ void __launch_bounds__(512, 1)
+constexpr int SNC = 16;   // columns per CTA of slice_nmajor512_kernel: 256 threads, two CTAs per SM overlap their load and store phases
+__global__ void __launch_bounds__(SNC * 16, 2)
 slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, int CB, int* __restrict__ ex, double* __restrict__ scale,
                        double extra, int8_t* __restrict__ out, int RBA, double* __restrict__ scaleA, int8_t* __restrict__ outA,
                        int* __restrict__ err, const double* __restrict__ rsc, long s_rsc) {
   constexpr int K = 512, KB = K / EKC;
-  __shared__ double red[16][33];
-  const int z = blockIdx.y, lane = threadIdx.x & 31, kq = threadIdx.x >> 5;
-  const int n = blockIdx.x * 32 + lane, cb = n / EBN, nn = n % EBN;
+  __shared__ double red[16][SNC + 1];
+  const int z = blockIdx.y, lane = threadIdx.x % SNC, kq = threadIdx.x / SNC;
+  const int n = blockIdx.x * SNC + lane, cb = n / EBN, nn = n % EBN;
   double x[32];
   double mx = 0.0;
   bool bad = false;
@@ -325,9 +326,9 @@ standardize_slice_kernel(PanelView pv, int NP, int P, int tau0, const int* __res
   }
 }
 
-// The same for NP <= 512 in ONE pass over the gathered panel rows: a CTA owns 32 output columns, thread = (column,
+// The same for NP <= 512 in ONE pass over the gathered panel rows: a CTA owns SNC output columns, thread = (column,
 // group of 32 rows) keeps its values in registers from the statistics to the digits (like slice_nmajor512_kernel).
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(SNC * 16, 2)
 standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __restrict__ date_t, const int* __restrict__ sel,
                             const int* __restrict__ nsel, BatchVecs v, int8_t* __restrict__ out, long slab_bytes,
                             double* __restrict__ scale_out, int* __restrict__ err) {
@@ -336,14 +337,14 @@ standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __
   const int ntau = gridDim.y, nB = gridDim.z - ntau + 1;
   const int b = (int)blockIdx.z + (int)blockIdx.y - (ntau - 1), tau = tau0 + blockIdx.y;
   if (b < 0 || b >= nB) return;
-  const int lane = threadIdx.x & 31, rg = threadIdx.x >> 5;      // rows rg * 32 .. rg * 32 + 31
-  const int j = blockIdx.x * 32 + lane;                           // output column (0 = constant)
+  const int lane = threadIdx.x % SNC, rg = threadIdx.x / SNC;    // rows rg * 32 .. rg * 32 + 31
+  const int j = blockIdx.x * SNC + lane;                           // output column (0 = constant)
   const int n = nsel[b], t = date_t[b] - tau;
   const int CB = (P + EBN - 1) / EBN, KB = NP / EKC;
   // row factor sqrt(lambda_i) / vol_scale_i once per CTA (the FP64 kernel applies the two factors one after the other:
   // one rounding more, far below the digit resolution); non-finite factors are caught here, non-finite signals by the
   // sum of squares below
-  __shared__ double s_rf[512], s_red[16][33];
+  __shared__ double s_rf[512], s_red[16][SNC + 1];
   __shared__ int s_sel[512];
   const double* __restrict__ vs = pv.vol_scale + (long)t * pv.N;
   bool bad = false;
@@ -716,7 +717,7 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
                 cudaStream_t s) {
   if (K == 512) {
     // 64-column blocks are written by two CTAs of 32 columns; the padded half of the last block must be zero-filled too
-    slice_nmajor512_kernel<<<dim3(2 * ceil_div(N, EBN), batch), 512, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, kBScale,
+    slice_nmajor512_kernel<<<dim3((EBN / SNC) * ceil_div(N, EBN), batch), SNC * 16, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, kBScale,
                                                                              out, 0, nullptr, nullptr, err, nullptr, 0);
     PFML_CHECK_LAUNCH();
     return 0;
@@ -732,8 +733,8 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
 int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
                         double* sa, int* err, cudaStream_t s, const double* row_scale, long s_row_scale) {
   const int CB = ceil_div(C, EBN), RBA = ceil_div(C, EBM);
-  const int blocks = outA ? 4 * RBA : 2 * CB;          // 32 columns per CTA; the padded tail of the last block is zero-filled
-  slice_nmajor512_kernel<<<dim3(blocks, batch), 512, 0, s>>>(X, ld, sX, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err, row_scale, s_row_scale);
+  const int blocks = outA ? (EBM / SNC) * RBA : (EBN / SNC) * CB;   // SNC columns per CTA; the padded tail of the last block is zero-filled
+  slice_nmajor512_kernel<<<dim3(blocks, batch), SNC * 16, 0, s>>>(X, ld, sX, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err, row_scale, s_row_scale);
   PFML_CHECK_LAUNCH();
   return 0;
 }
@@ -745,7 +746,7 @@ int emu_standardize_slices(const PanelView& pv, int B, int NP, int P, int tau0, 
   const int CB = ceil_div(P, EBN);
   dim3 grid(CB, ntau, B);
   if (NP <= 512) {
-    standardize_slice512_kernel<<<dim3(2 * CB, ntau, B + ntau - 1), 512, 0, s>>>(pv, NP, P, tau0, date_t, sel, nsel, v, out,
+    standardize_slice512_kernel<<<dim3((EBN / SNC) * CB, ntau, B + ntau - 1), SNC * 16, 0, s>>>(pv, NP, P, tau0, date_t, sel, nsel, v, out,
                                                                       (long)emu_b_slices_bytes(B, NP, P), scale_out, err);
     PFML_CHECK_LAUNCH();
     return 0;
