@@ -105,7 +105,11 @@ extern "C" int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_m
     }
     if (left > 0) sched.push_back(left);
   } else {
-    if (chunk <= 0) chunk = B <= 40 ? B : (B + 5) / 6;      // measured best on B200 (tools/e2e_chunk_sweep.py)
+    // measured best on B200 (tools/e2e_chunk_sweep.py): B / 6 when every output is downloaded (29 MB per date: the copy
+    // engine must start early and stay busy), B / 3 when only r_tilde and denom are (8 MB per date: larger chunks
+    // compute more efficiently)
+    const bool all_outputs = risk || tc || signal_t;
+    if (chunk <= 0) chunk = B <= 40 ? B : (all_outputs ? (B + 5) / 6 : (B + 2) / 3);
     for (int b0 = 0; b0 < B; b0 += chunk) sched.push_back((B - b0) < chunk ? (B - b0) : chunk);
   }
   chunk = 0;
