@@ -88,3 +88,25 @@ def test_date_steps_same_with_and_without_emulation():
         assert x["status"] == 0 and y["status"] == 0
         for key in ("r_tilde", "denom", "risk", "tc", "signal_t"):
             assert relerr(x[key], y[key]) < 1e-11, key
+
+
+@pytest.mark.parametrize("N,p,months", [(40, 4, [13]), (70, 2, [12, 13]), (130, 6, [14]), (500, 20, [12])])
+def test_date_steps_odd_shapes_both_paths(N, p, months):
+    """Tiny universes / feature counts (one k-stage, one tile, P < 64) and n = 500 with few features: the INT8 path
+    (direct form, fused standardise + digits, symmetric a9 products at n = 512) against the DMMA path."""
+    from conftest import relerr
+    from pfml_b200 import _lib, device, synthetic
+    lib = _lib.load()
+    panel = synthetic.make_panel(N=N, T=15, p=p, seed=40 + N, ragged=0.02)
+    try:
+        lib.pfml_set_emulation(1)
+        a = device.date_steps(panel, months)
+        lib.pfml_set_emulation(0)
+        b = device.date_steps(panel, months)
+    finally:
+        lib.pfml_set_emulation(1)
+    for x, y in zip(a, b):
+        assert x["status"] == 0 and y["status"] == 0
+        for key in ("r_tilde", "denom", "risk", "tc", "signal_t"):
+            assert relerr(x[key], y[key]) < 1e-10, (key, relerr(x[key], y[key]))
+        assert (x["denom"] == x["denom"].T).all()
