@@ -158,13 +158,16 @@ int pfml_dgemm_batched(int trans_a, int trans_b, int M, int N, int K, double alp
  * below the largest element of each row of A / column of B are kept, measured 3e-15 relative to the DMMA product
  * at K = 512 (no reference
  * counterpart; it is how the date-step runs its n x n x P products).  Needs K % 64 == 0.  status[0] gets bit 3 on an
- * internal time-out, bit 4 if an operand holds NaN/Inf (they cannot be sliced).  pfml_set_emulation(0) makes
- * pfml_date_steps use the DMMA kernel for those products instead (default 1, or env PFML_EMULATE_FP64). */
+ * internal time-out, bit 4 if an operand holds NaN/Inf (they cannot be sliced).
+ * pfml_set_emulation(mode) selects how pfml_date_steps runs its products (default 1, or env PFML_EMULATE_FP64):
+ *   0 = FP64 DMMA kernel; 1 = INT8 path with all 7 digits (1e-13 of the DMMA result); 2 = INT8 path with 6 digits for the
+ *   products whose errors do not compound (n x P sums, solves, a9; the chain keeps 7): 6 % faster, 7e-12 of the DMMA
+ *   result at N = 500 and 2e-11 at N = 3000 (tools/emu_modes.py). */
 size_t pfml_dgemm_emulated_workspace_bytes(int M, int N, int K, int batch);
 int pfml_dgemm_emulated(int M, int N, int K, double alpha, const double* A, long lda, long sA, const double* B, long ldb,
                         long sB, double beta, double* D, long ldd, long sD, int batch, int* status, void* workspace,
                         size_t workspace_bytes, void* stream);
-void pfml_set_emulation(int on);
+void pfml_set_emulation(int mode);
 
 /* Batched inverse of well-conditioned n x n matrices by recursive Schur-complement blocks (np.linalg.inv at
  * General_functions.py:960).  A [B][n][n] -> Ainv [B][n][n]. */

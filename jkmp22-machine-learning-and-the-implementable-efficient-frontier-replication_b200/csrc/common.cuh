@@ -82,6 +82,7 @@ struct EmuExtra {
   double* D2 = nullptr; const double* E2 = nullptr; long ld2 = 0, s2 = 0;
   const double* az = nullptr; long s_az = 0;   // per-matrix factor on alpha
   bool sym = false;                            // symmetric result: only the upper triangle is written, the caller mirrors it
+  int digits = 0;                              // leading base-256 digits of both operands to use (0 = all 7; 6 = 21 products)
 };
 int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
                         double* sa, int* err, cudaStream_t s, const double* row_scale = nullptr, long s_row_scale = 0);

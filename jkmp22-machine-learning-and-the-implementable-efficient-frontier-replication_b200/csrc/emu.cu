@@ -482,6 +482,9 @@ struct EmuP {
 constexpr int EPI_G = 4;                                      // column groups of the epilogue -> 4 * EPI_G epilogue warps
 constexpr int EMU_THREADS = 128 + 128 * EPI_G;
 
+// ND <= ES: number of leading digits of both operands that are used (ND (ND + 1) / 2 products).  The operand layout
+// always holds ES digits per stage; a balanced-digit number cut after ND digits is that number rounded to ND digits.
+template <int ND>
 __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
@@ -522,11 +525,11 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
         if (!mbar_wait(smem_u32(&empty_bar[s]), (uint32_t)(((it / ESTAGES) & 1) ^ 1))) { atomicOr(p.err, 1); return; }
         if (elect_one()) {
           const uint32_t fb = smem_u32(&full_bar[s]);
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(EA_STAGE + EB_STAGE) : "memory");
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(ND * (EBM + EBN) * EKC) : "memory");
           asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                       ::"r"(smem_u32(sA + s * EA_STAGE)), "l"(a_src + (long)kc * EA_STAGE), "r"(EA_STAGE), "r"(fb) : "memory");
+                       ::"r"(smem_u32(sA + s * EA_STAGE)), "l"(a_src + (long)kc * EA_STAGE), "r"(ND * EBM * EKC), "r"(fb) : "memory");
           asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                       ::"r"(smem_u32(sB + s * EB_STAGE)), "l"(b_src + (long)kc * EB_STAGE), "r"(EB_STAGE), "r"(fb) : "memory");
+                       ::"r"(smem_u32(sB + s * EB_STAGE)), "l"(b_src + (long)kc * EB_STAGE), "r"(ND * EBN * EKC), "r"(fb) : "memory");
         }
         __syncwarp();
       }
@@ -554,11 +557,11 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
 #pragma unroll
           for (int kk = 0; kk < EKC / 32; kk++) {
 #pragma unroll
-            for (int i = 0; i < ETS; i++) utccp_128x32(tbase + EACOL + i * 8, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4));
+            for (int i = 0; i < (ETS < ND ? ETS : ND); i++) utccp_128x32(tbase + EACOL + i * 8, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4));
 #pragma unroll
-            for (int i = 0; i < ES; i++)
+            for (int i = 0; i < ND; i++)
 #pragma unroll
-              for (int j = 0; j < ES - i; j++) {
+              for (int j = 0; j < ND - i; j++) {
                 const uint32_t acc = (kk > 0 || i > 0) ? 1u : 0u;
                 if (i < ETS) umma_i8_ts(tbase + (i + j) * EBN, tbase + EACOL + i * 8, db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, acc);
                 else umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
@@ -569,11 +572,11 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
 #pragma unroll
           for (int kk = 0; kk < EKC / 32; kk++) {
 #pragma unroll
-            for (int i = 0; i < ETS; i++) utccp_128x32(tbase + EACOL + i * 8, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4));
+            for (int i = 0; i < (ETS < ND ? ETS : ND); i++) utccp_128x32(tbase + EACOL + i * 8, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4));
 #pragma unroll
-            for (int i = 0; i < ES; i++)
+            for (int i = 0; i < ND; i++)
 #pragma unroll
-              for (int j = 0; j < ES - i; j++) {
+              for (int j = 0; j < ND - i; j++) {
                 if (i < ETS) umma_i8_ts(tbase + (i + j) * EBN, tbase + EACOL + i * 8, db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, 1u);
                 else umma_i8(tbase + (i + j) * EBN, da0 + ((i * (EBM * EKC) + kk * 2 * ELBO) >> 4),
                              db0 + ((j * (EBN * EKC) + kk * 2 * ELBO) >> 4), idesc, 1u);
@@ -595,7 +598,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
     const int q = warp & 3, g = (warp - 4) >> 2;
     double* stg = reinterpret_cast<double*>(smem + ESTAGES * (EA_STAGE + EB_STAGE)) + (warp - 4) * (32 * 9);   // 32 x 8 (+1 pad)
     constexpr int GC = EBN / EPI_G;                 // columns per warp
-    const int shl = p.q - 24, shr = 8 * (ES - 1) - p.q;
+    const int shl = p.q - 24, shr = 8 * (ND - 1) - p.q;
     const long long rnd = shr > 0 ? (1ll << (shr - 1)) : 0;   // round the dropped low bits to nearest
     int tl = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
@@ -616,9 +619,9 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
       long long S[GC];
 #pragma unroll
       for (int c0 = 0; c0 < GC; c0 += 8) {
-        uint32_t v[ES][8];
+        uint32_t v[ND][8];
 #pragma unroll
-        for (int d = 0; d < ES; d++)
+        for (int d = 0; d < ND; d++)
           asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                        : "=r"(v[d][0]), "=r"(v[d][1]), "=r"(v[d][2]), "=r"(v[d][3]), "=r"(v[d][4]), "=r"(v[d][5]), "=r"(v[d][6]), "=r"(v[d][7])
                        : "r"(tbase + ((uint32_t)(q * 32) << 16) + d * EBN + g * GC + c0));
@@ -631,7 +634,7 @@ __global__ void __launch_bounds__(EMU_THREADS, 1) emu_gemm_kernel(const EmuP p) 
         for (int c = 0; c < 8; c++) {
           long long hi = 0, lo = 0;
 #pragma unroll
-          for (int d = 0; d < ES; d++) {
+          for (int d = 0; d < ND; d++) {
             if (d < 4) hi = hi * 256 + (long long)(int32_t)v[d][c];
             else lo = lo * 256 + (long long)(int32_t)v[d][c];
           }
@@ -787,14 +790,20 @@ int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const doubl
   int vb = 0;
   while ((1.01 * K * 16384.0) >= (double)(1ll << vb)) vb++;
   p.q = 62 - vb;
-  if (p.q > 8 * (ES - 1)) p.q = 8 * (ES - 1);
+  const int digits = (x.digits >= 4 && x.digits < ES) ? x.digits : ES;
+  if (digits != ES && digits != 6) {
+    set_error("emu_mma: %d digits not built (6 or %d)", digits, ES);
+    return -2;
+  }
+  if (p.q > 8 * (digits - 1)) p.q = 8 * (digits - 1);
   constexpr size_t smem = (size_t)ESTAGES * (EA_STAGE + EB_STAGE) + (size_t)(4 * EPI_G) * 32 * 9 * sizeof(double);
   static bool cfg[64] = {};
   static int n_sm[64] = {};
   int dev = 0;
   PFML_CUDA_OK(cudaGetDevice(&dev));
   if (!cfg[dev & 63]) {
-    PFML_CUDA_OK(cudaFuncSetAttribute(emu_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PFML_CUDA_OK(cudaFuncSetAttribute(emu_gemm_kernel<ES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PFML_CUDA_OK(cudaFuncSetAttribute(emu_gemm_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     PFML_CUDA_OK(cudaDeviceGetAttribute(&n_sm[dev & 63], cudaDevAttrMultiProcessorCount, dev));
     cfg[dev & 63] = true;
   }
@@ -802,7 +811,8 @@ int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const doubl
   const long want = n_sm[dev & 63];                       // persistent: one CTA per SM (it owns the SM's whole TMEM)
   const int grid = (int)(tiles < want ? tiles : want);
   prof_begin(-2, s);
-  emu_gemm_kernel<<<grid, EMU_THREADS, smem, s>>>(p);
+  if (digits == ES) emu_gemm_kernel<ES><<<grid, EMU_THREADS, smem, s>>>(p);
+  else emu_gemm_kernel<6><<<grid, EMU_THREADS, smem, s>>>(p);
   PFML_CHECK_LAUNCH();
   prof_end(-2, s, 2.0 * M * (double)N * K * batch, 0.0);
   return 0;

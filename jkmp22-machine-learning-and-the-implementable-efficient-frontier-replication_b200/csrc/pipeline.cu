@@ -187,7 +187,8 @@ static int g_use_emu = -1;
 static bool use_emu() {
   if (g_use_emu < 0) {
     const char* e = getenv("PFML_EMULATE_FP64");
-    g_use_emu = e ? (atoi(e) != 0) : 1;
+    g_use_emu = e ? atoi(e) : 1;
+    if (g_use_emu < 0 || g_use_emu > 2) g_use_emu = 1;
   }
   return g_use_emu != 0;
 }
@@ -372,8 +373,13 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   }
   const bool emu = use_emu() && emu_shape_ok(NP, P, NP);
   const bool emu_nn = emu && emu_shape_ok(NP, NP, NP);
+
   // direct form of the n x P sums (INT8 path): Z = sum_k B~_k S~_{k+1} term by term next to the chain products
   const bool direct = emu_nn && lb - 1 <= 16 && w.chain != nullptr;
+  // mode 2 (direct form only): the products whose errors do not compound (n x P sums, solves, a9) use 6 of the 7
+  // digits (21 products); the chain products, whose results are multiplied on, always use all 7
+  EmuExtra xq;
+  xq.digits = (g_use_emu == 2 && direct) ? 6 : 0;
   const double* emu_a_cur = nullptr;       // whose slices currently sit in w.eAs
   if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int), s));
   // ---- a6 standardise (after m~: the signal slabs reuse the quadrature stack's memory) -------------
@@ -396,7 +402,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
         emu_a_cur = A;
       }
       PFML_TRY(emu_slice_b(X, ldP, sX, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
-      return emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, alpha, rs, s_rs, E ? 1.0 : 0.0, E, ldP, sE, D, ldP, sD, w.eerr, s);
+      return emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, alpha, rs, s_rs, E ? 1.0 : 0.0, E, ldP, sE, D, ldP, sD, xq, w.eerr, s);
     }
     GemmP g;
     g.A = A; g.lda = NP; g.sA = NN; g.B = X; g.ldb = ldP; g.sB = sX; g.D = D; g.ldd = ldP; g.sD = sD;
@@ -429,8 +435,8 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       {
         ProfScope ps(T_HORNER, s);
         const double* E = (k == 1) ? St(1) : Z;     // slab k + 1 was sliced by the standardise kernel
-        PFML_TRY(emu_mma(w.eAs, w.esa, w.eSs + (size_t)(k - 1) * slabS, w.eSsb + (size_t)(k - 1) * B * P, NP, P, NP, B, 1.0, nullptr, 0,
-                         1.0, E, ldP, (k == 1) ? sSt : nP, Z, ldP, nP, w.eerr, s));
+        PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eSs + (size_t)(k - 1) * slabS, w.eSsb + (size_t)(k - 1) * B * P, NP, P, NP, B, 1.0, nullptr,
+                            0, 1.0, E, ldP, (k == 1) ? sSt : nP, Z, ldP, nP, xq, w.eerr, s));
       }
     }
     // NOTE: in iteration k the A slices are those of B~_k (sliced before the chain step overwrote Bt_a's role)
@@ -454,10 +460,10 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
         PFML_TRY(row_scale(B, NP, P, ldP, nP, Z, gv(0), sg, ZG, ldP, nP, s));
         PFML_TRY(emu_slice_b(ZG, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
       }
-      PFML_TRY(emu_mma(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, St(0), ldP, sSt, w.Nn, ldP, nP, w.eerr, s));
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, St(0), ldP, sSt, w.Nn, ldP, nP, xq, w.eerr, s));
       PFML_TRY(emu_slice_a(B11, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
-      PFML_TRY(emu_mma(w.eAs, w.esa, w.eSs + (size_t)(lb - 1) * slabS, w.eSsb + (size_t)(lb - 1) * B * P, NP, P, NP, B, 1.0, nullptr, 0,
-                       1.0, Z, ldP, nP, w.Nl1, ldP, nP, w.eerr, s));
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eSs + (size_t)(lb - 1) * slabS, w.eSsb + (size_t)(lb - 1) * B * P, NP, P, NP, B, 1.0, nullptr, 0,
+                          1.0, Z, ldP, nP, w.Nl1, ldP, nP, xq, w.eerr, s));
     }
   } else {
   // ---- a7 chain of n x n products (tilde domain) ------------------------------------------------
@@ -590,13 +596,13 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       PFML_TRY(emu_slice_nmajor512(w.OM, ldP, sStack, P, B, nullptr, nullptr, nullptr, w.eAs, w.esa, w.eerr, s));
       PFML_TRY(emu_slice_nmajor512(w.BS, ldP, sStack, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s));
       EmuExtra xr;
-      xr.sym = true;
+      xr.sym = true; xr.digits = xq.digits;
       PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 1.0, risk, P, (long)P * P, risk, P, (long)P * P, xr,
                           w.eerr, s));
       // tc = w omega~_chg' omega~_chg ; denom = risk + tc
       PFML_TRY(emu_slice_nmajor512(w.OMC, ldP, nP, P, B, w.eBs, w.esb, w.eex, w.eAs, w.esa, w.eerr, s));
       EmuExtra xt;
-      xt.sym = true; xt.az = w.v.scal + 0; xt.s_az = NSCAL;
+      xt.sym = true; xt.az = w.v.scal + 0; xt.s_az = NSCAL; xt.digits = xq.digits;
       PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, tc, P, (long)P * P, xt, w.eerr, s));
       PFML_TRY(sym_finish(B, P, risk, tc, denom, s));        // denom = risk + tc; lower triangles = copies of the upper
       if (status) {
@@ -817,7 +823,7 @@ int pfml_dgemm_emulated(int M, int N, int K, double alpha, const double* A, long
   return 0;
 }
 
-void pfml_set_emulation(int on) { g_use_emu = on != 0; }
+void pfml_set_emulation(int on) { g_use_emu = (on < 0 || on > 2) ? 1 : on; }
 
 namespace {
 __global__ void pad_identity_kernel(int n, int NP, const double* __restrict__ A, double* __restrict__ Wk) {

@@ -110,3 +110,27 @@ def test_date_steps_odd_shapes_both_paths(N, p, months):
         for key in ("r_tilde", "denom", "risk", "tc", "signal_t"):
             assert relerr(x[key], y[key]) < 1e-10, (key, relerr(x[key], y[key]))
         assert (x["denom"] == x["denom"].T).all()
+
+
+def test_date_steps_six_digit_mode():
+    """pfml_set_emulation(2): 6 of the 7 digits for the products whose errors do not compound (n x P sums, solves, a9).
+    Still far inside the 1e-8 tolerance: measured 7e-12 against the DMMA path at N = 500, p = 1024."""
+    from conftest import relerr
+    from pfml_b200 import _lib, device, synthetic
+    import pfml_oracle as O
+    lib = _lib.load()
+    panel = synthetic.make_panel(N=500, T=14, p=64, seed=52, ragged=0.02)
+    rff_x = O.rff(panel.feats.reshape(-1, panel.feats.shape[2]), panel.W).reshape(panel.feats.shape[0], panel.feats.shape[1], -1)
+    vs = O.vol_scale_panel(panel)
+    try:
+        lib.pfml_set_emulation(2)
+        a = device.date_steps(panel, [12])
+        lib.pfml_set_emulation(0)
+        b = device.date_steps(panel, [12])
+    finally:
+        lib.pfml_set_emulation(1)
+    o = O.date_step(panel, 12, rff_x, vs)
+    for key in ("r_tilde", "denom", "risk", "tc", "signal_t"):
+        assert relerr(a[0][key], b[0][key]) < 1e-9, (key, relerr(a[0][key], b[0][key]))
+        assert relerr(a[0][key], o[key]) < 1e-8, key
+    assert a[0]["status"] == 0
