@@ -84,8 +84,9 @@ struct EmuExtra {
   bool sym = false;                            // symmetric result: only the upper triangle is written, the caller mirrors it
   int digits = 0;                              // leading base-256 digits of both operands to use (0 = all 7; 6 = 21 products)
 };
-int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
-                        double* sa, int* err, cudaStream_t s, const double* row_scale = nullptr, long s_row_scale = 0);
+int emu_slice_nmajor512(const double* X, long ld, long sX, int K, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
+                        double* sa, int* err, cudaStream_t s, const double* row_scale = nullptr, long s_row_scale = 0,
+                        int* zflag = nullptr /* [batch]: non-finite operand flagged per matrix instead of through err */);
 int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const double* sb, int M, int N, int K, int batch, double alpha,
                const double* rs, long s_rs, double beta, const double* E, long lde, long sE, double* D, long ldd, long sD,
                const EmuExtra& x, int* err, cudaStream_t s);

@@ -105,32 +105,36 @@ __global__ void slice_kmajor_kernel(const double* __restrict__ X, long ld, long 
   }
 }
 
-// The same for K == 512 in one pass over the data.  A CTA owns 8 rows: warp w takes the 64-byte k chunk w of all of
-// them, lane = (row r, 16-element group c), so that one store instruction of a warp writes four whole 8 x 16 B core
-// matrices (512 contiguous bytes) of the operand layout; the row maxima meet in shared memory.
+// The same for K <= 1024 (K % 64 == 0) in one pass over the data.  A CTA owns 8 rows: warp w takes the 64-byte k chunks w
+// and w + 8 of all of them, lane = (row r, 16-element group c), so that one store instruction of a warp writes four
+// whole 8 x 16 B core matrices (512 contiguous bytes) of the operand layout; the row maxima meet in shared memory.
+constexpr int ONEPASS_KMAX = 1024;
 template <int BR>
 __global__ void __launch_bounds__(256)
-slice_kmajor512_kernel(const double* __restrict__ X, long ld, long sX, int R, int8_t* __restrict__ out,
+slice_kmajor512_kernel(const double* __restrict__ X, long ld, long sX, int R, int K, int8_t* __restrict__ out,
                        double* __restrict__ scale, double extra, int* __restrict__ err) {
-  constexpr int K = 512, KB = K / EKC;
   static_assert(EKC == 64, "one warp per 64-byte k chunk");
   __shared__ double s_mx[8][8];
   const int z = blockIdx.y, w = threadIdx.x >> 5, lane = threadIdx.x & 31, r = lane & 7, c = lane >> 3;
-  const int row = blockIdx.x * 8 + r;
+  const int row = blockIdx.x * 8 + r, KB = K / EKC;
   const int RB = (R + BR - 1) / BR;
   constexpr long STAGE = (long)ES * BR * EKC;
-  double x[16];
+  double x[2][16];
   double mx = 0.0;
   bool bad = false;
-  if (row < R) {
-    const double2* a = reinterpret_cast<const double2*>(X + (long)z * sX + (long)row * ld + w * EKC + c * 16);
 #pragma unroll
-    for (int k = 0; k < 8; k++) { const double2 v = a[k]; x[2 * k] = v.x; x[2 * k + 1] = v.y; }
+  for (int h = 0; h < 2; h++) {
+    const int ch = w + 8 * h;
+    if (row < R && ch < KB) {
+      const double2* a = reinterpret_cast<const double2*>(X + (long)z * sX + (long)row * ld + ch * EKC + c * 16);
 #pragma unroll
-    for (int k = 0; k < 16; k++) { const double v = fabs(x[k]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
-  } else {
+      for (int k = 0; k < 8; k++) { const double2 v = a[k]; x[h][2 * k] = v.x; x[h][2 * k + 1] = v.y; }
 #pragma unroll
-    for (int k = 0; k < 16; k++) x[k] = 0.0;
+      for (int k = 0; k < 16; k++) { const double v = fabs(x[h][k]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 16; k++) x[h][k] = 0.0;
+    }
   }
   if (bad) atomicOr(err, 16);
   mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
@@ -142,8 +146,11 @@ slice_kmajor512_kernel(const double* __restrict__ X, long ld, long sX, int R, in
   const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
   if (w == 0 && c == 0 && row < R) scale[(long)z * R + row] = scalbn(extra, e);
   if (row >= RB * BR) return;
-  int8_t* base = out + (((long)z * RB + row / BR) * KB + w) * STAGE;
-  slice16(x, e, base + canon(row % BR, c * 16), (long)BR * EKC);
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const int ch = w + 8 * h;
+    if (ch < KB) slice16(x[h], e, out + (((long)z * RB + row / BR) * KB + ch) * STAGE + canon(row % BR, c * 16), (long)BR * EKC);
+  }
 }
 
 // B-type operand: X [K][C] with C contiguous (ld), scaled per column, blocks of 64 columns.
@@ -178,13 +185,13 @@ slice_nmajor_kernel(const double* __restrict__ X, long ld, long sX, int K, int C
 // N-major operand X [512][C] in one pass: a CTA owns 32 columns x all 512 k (thread = column, 32 consecutive k held in
 // registers), the column maxima go through shared memory, no separate exponent kernel.  Writes the B-type slices
 // (64-column blocks, `out`) and / or the A-type slices of X' (128-row blocks, `outA`: X' as the left operand).
-constexpr int SNC = 16;   // columns per CTA of slice_nmajor512_kernel: 256 threads, two CTAs per SM overlap their load and store phases
-__global__ void __launch_bounds__(SNC * 16, 2)
-slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, int CB, int* __restrict__ ex, double* __restrict__ scale,
+constexpr int SNC = 16;   // columns per CTA of the one-pass N-major kernels: 256 threads at K = 512, two CTAs per SM overlap their load and store phases
+__global__ void __launch_bounds__(SNC * 32)
+slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int K, int C, int CB, int* __restrict__ ex, double* __restrict__ scale,
                        double extra, int8_t* __restrict__ out, int RBA, double* __restrict__ scaleA, int8_t* __restrict__ outA,
-                       int* __restrict__ err, const double* __restrict__ rsc, long s_rsc) {
-  constexpr int K = 512, KB = K / EKC;
-  __shared__ double red[16][SNC + 1];
+                       int* __restrict__ err, const double* __restrict__ rsc, long s_rsc, int* __restrict__ zflag) {
+  const int KB = K / EKC, NKQ = K / 32;                  // blockDim.x = SNC * NKQ (K <= 1024: up to 512 threads)
+  __shared__ double red[32][SNC + 1];
   const int z = blockIdx.y, lane = threadIdx.x % SNC, kq = threadIdx.x / SNC;
   const int n = blockIdx.x * SNC + lane, cb = n / EBN, nn = n % EBN;
   double x[32];
@@ -205,11 +212,12 @@ slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int C, in
 #pragma unroll
     for (int j = 0; j < 32; j++) x[j] = 0.0;
   }
-  if (bad) atomicOr(err, 16);
+  // a non-finite operand is an error (status bit 4) unless the caller asked for a per-matrix flag instead (zflag: the
+  // reference's own NaN semantics, quirk Q8, are then reproduced by the caller)
+  if (bad) { if (zflag) atomicOr(zflag + z, 1); else atomicOr(err, 16); }
   red[kq][lane] = mx;
   __syncthreads();
-#pragma unroll
-  for (int j = 0; j < 16; j++) mx = fmax(mx, red[j][lane]);
+  for (int j = 0; j < NKQ; j++) mx = fmax(mx, red[j][lane]);
   const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
   if (kq == 0 && n < C) {
     if (out) { ex[(long)z * C + n] = e; scale[(long)z * C + n] = scalbn(extra, e); }
@@ -326,9 +334,9 @@ standardize_slice_kernel(PanelView pv, int NP, int P, int tau0, const int* __res
   }
 }
 
-// The same for NP <= 512 in ONE pass over the gathered panel rows: a CTA owns SNC output columns, thread = (column,
+// The same for NP <= 1024 in ONE pass over the gathered panel rows: a CTA owns SNC output columns, thread = (column,
 // group of 32 rows) keeps its values in registers from the statistics to the digits (like slice_nmajor512_kernel).
-__global__ void __launch_bounds__(SNC * 16, 2)
+__global__ void __launch_bounds__(SNC * 32)
 standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __restrict__ date_t, const int* __restrict__ sel,
                             const int* __restrict__ nsel, BatchVecs v, int8_t* __restrict__ out, long slab_bytes,
                             double* __restrict__ scale_out, int* __restrict__ err) {
@@ -344,8 +352,9 @@ standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __
   // row factor sqrt(lambda_i) / vol_scale_i once per CTA (the FP64 kernel applies the two factors one after the other:
   // one rounding more, far below the digit resolution); non-finite factors are caught here, non-finite signals by the
   // sum of squares below
-  __shared__ double s_rf[512], s_red[16][SNC + 1];
-  __shared__ int s_sel[512];
+  __shared__ double s_rf[ONEPASS_KMAX], s_red[32][SNC + 1];     // blockDim.x = SNC * (NP / 32)
+  __shared__ int s_sel[ONEPASS_KMAX];
+  const int NRG = NP / 32;
   const double* __restrict__ vs = pv.vol_scale + (long)t * pv.N;
   bool bad = false;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -373,8 +382,7 @@ standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __
   __syncthreads();
   double mean = 0.0;
   if (j > 0) {
-#pragma unroll
-    for (int q = 0; q < 16; q++) mean += s_red[q][lane];
+    for (int q = 0; q < NRG; q++) mean += s_red[q][lane];
     mean = mean / (double)n;
   }
   __syncthreads();
@@ -393,13 +401,11 @@ standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __
   s_red[rg][lane] = part;
   __syncthreads();
   double ss = 0.0;
-#pragma unroll
-  for (int q = 0; q < 16; q++) ss += s_red[q][lane];
+  for (int q = 0; q < NRG; q++) ss += s_red[q][lane];
   __syncthreads();
   s_red[rg][lane] = mx;
   __syncthreads();
-#pragma unroll
-  for (int q = 0; q < 16; q++) mx = fmax(mx, s_red[q][lane]);
+  for (int q = 0; q < NRG; q++) mx = fmax(mx, s_red[q][lane]);
   const double scale = real ? ((j == 0) ? sqrt(1.0 / (double)n) : sqrt(1.0 / ss)) : 0.0;
   mx *= scale;                                               // largest |value| up to rounding (digits tolerate 1.98 * 2^e)
   bad |= real && !(ss <= 1.7976931348623157e308 && mx <= 1.7976931348623157e308);
@@ -707,8 +713,8 @@ bool emu_shape_ok(int M, int N, int K) { return M > 0 && N > 0 && K >= EKC && K 
 // A [M][K] (K contiguous) -> slices + row scales 2^ea
 int emu_slice_a(const double* A, long lda, long sA, int M, int K, int batch, int8_t* out, double* scale, int* err, cudaStream_t s) {
   const int rows = ceil_div(M, EBM) * EBM;
-  if (K == 512 && (lda % 2) == 0 && (sA % 2) == 0 && ((uintptr_t)A % 16) == 0)
-    slice_kmajor512_kernel<EBM><<<dim3(ceil_div(rows, 8), batch), 256, 0, s>>>(A, lda, sA, M, out, scale, 1.0, err);
+  if (K <= ONEPASS_KMAX && (lda % 2) == 0 && (sA % 2) == 0 && ((uintptr_t)A % 16) == 0)
+    slice_kmajor512_kernel<EBM><<<dim3(ceil_div(rows, 8), batch), 256, 0, s>>>(A, lda, sA, M, K, out, scale, 1.0, err);
   else
     slice_kmajor_kernel<EBM><<<dim3(ceil_div(rows, 8), batch), 256, 0, s>>>(A, lda, sA, M, K, out, scale, 1.0, err);
   PFML_CHECK_LAUNCH();
@@ -718,10 +724,10 @@ int emu_slice_a(const double* A, long lda, long sA, int M, int K, int batch, int
 // B [K][N] (N contiguous) -> slices + column scales 2^(eb - 14); ex [batch][N] is int scratch
 int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int8_t* out, double* scale, int* ex, int* err,
                 cudaStream_t s) {
-  if (K == 512) {
-    // 64-column blocks are written by two CTAs of 32 columns; the padded half of the last block must be zero-filled too
-    slice_nmajor512_kernel<<<dim3((EBN / SNC) * ceil_div(N, EBN), batch), SNC * 16, 0, s>>>(B, ldb, sB, N, ceil_div(N, EBN), ex, scale, kBScale,
-                                                                             out, 0, nullptr, nullptr, err, nullptr, 0);
+  if (K <= ONEPASS_KMAX) {
+    // 64-column blocks are written by several CTAs of SNC columns; the padded part of the last block is zero-filled too
+    slice_nmajor512_kernel<<<dim3((EBN / SNC) * ceil_div(N, EBN), batch), SNC * (K / 32), 0, s>>>(B, ldb, sB, K, N, ceil_div(N, EBN), ex, scale, kBScale,
+                                                                             out, 0, nullptr, nullptr, err, nullptr, 0, nullptr);
     PFML_CHECK_LAUNCH();
     return 0;
   }
@@ -732,12 +738,17 @@ int emu_slice_b(const double* B, long ldb, long sB, int K, int N, int batch, int
   return 0;
 }
 
-// X [512][C] (C contiguous) -> B-type slices of X (outB, may be null) and / or A-type slices of X' (outA, may be null)
-int emu_slice_nmajor512(const double* X, long ld, long sX, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
-                        double* sa, int* err, cudaStream_t s, const double* row_scale, long s_row_scale) {
+// X [K][C] (C contiguous, K <= 1024) -> B-type slices of X (outB, may be null) and / or A-type slices of X' (outA, may be null)
+int emu_slice_nmajor512(const double* X, long ld, long sX, int K, int C, int batch, int8_t* outB, double* sb, int* ex, int8_t* outA,
+                        double* sa, int* err, cudaStream_t s, const double* row_scale, long s_row_scale, int* zflag) {
+  if (K > ONEPASS_KMAX || K % EKC != 0) {
+    set_error("emu_slice_nmajor512: K = %d (needs K %% 64 == 0 and K <= %d)", K, ONEPASS_KMAX);
+    return -2;
+  }
   const int CB = ceil_div(C, EBN), RBA = ceil_div(C, EBM);
   const int blocks = outA ? (EBM / SNC) * RBA : (EBN / SNC) * CB;   // SNC columns per CTA; the padded tail of the last block is zero-filled
-  slice_nmajor512_kernel<<<dim3(blocks, batch), SNC * 16, 0, s>>>(X, ld, sX, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err, row_scale, s_row_scale);
+  slice_nmajor512_kernel<<<dim3(blocks, batch), SNC * (K / 32), 0, s>>>(X, ld, sX, K, C, CB, ex, sb, kBScale, outB, RBA, sa, outA, err, row_scale,
+                                                                        s_row_scale, zflag);
   PFML_CHECK_LAUNCH();
   return 0;
 }
@@ -748,8 +759,8 @@ int emu_standardize_slices(const PanelView& pv, int B, int NP, int P, int tau0, 
                            const int* nsel, const BatchVecs& v, int8_t* out, double* scale_out, int* err, cudaStream_t s) {
   const int CB = ceil_div(P, EBN);
   dim3 grid(CB, ntau, B);
-  if (NP <= 512) {
-    standardize_slice512_kernel<<<dim3((EBN / SNC) * CB, ntau, B + ntau - 1), SNC * 16, 0, s>>>(pv, NP, P, tau0, date_t, sel, nsel, v, out,
+  if (NP <= ONEPASS_KMAX) {
+    standardize_slice512_kernel<<<dim3((EBN / SNC) * CB, ntau, B + ntau - 1), SNC * (NP / 32), 0, s>>>(pv, NP, P, tau0, date_t, sel, nsel, v, out,
                                                                       (long)emu_b_slices_bytes(B, NP, P), scale_out, err);
     PFML_CHECK_LAUNCH();
     return 0;

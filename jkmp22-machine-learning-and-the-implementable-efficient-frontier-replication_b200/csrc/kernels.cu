@@ -233,7 +233,8 @@ __global__ void chain_sum_kernel(int NP, int nk, ChainPtrs p, const double* __re
 
 // a9 finish for the upper-triangle products: denom = risk + tc, and risk, tc, denom mirrored into their lower triangles
 // (32 x 32 tiles through shared memory so that both the reads and the transposed writes are coalesced)
-__global__ void sym_finish_kernel(int P, double* __restrict__ risk, double* __restrict__ tc, double* __restrict__ denom) {
+__global__ void sym_finish_kernel(int P, double* __restrict__ risk, double* __restrict__ tc, double* __restrict__ denom,
+                                  const int* __restrict__ tc_nan) {
   __shared__ double tr[32][33], tt[32][33];
   const int bi = blockIdx.y, bj = blockIdx.x;
   if (bj < bi) return;
@@ -243,13 +244,18 @@ __global__ void sym_finish_kernel(int P, double* __restrict__ risk, double* __re
     const int r = bi * 32 + k, c = bj * 32 + tx;
     const bool ok = r < P && c < P;
     tr[k][tx] = ok ? risk[zo + (long)r * P + c] : 0.0;
-    tt[k][tx] = ok ? tc[zo + (long)r * P + c] : 0.0;
+    // tc_nan[date]: omega_chg held NaN (quirk Q8: missing growth rate at date d) -> every element of tc is NaN, as in
+    // the reference's dense product
+    tt[k][tx] = ok ? ((tc_nan && tc_nan[blockIdx.z]) ? __longlong_as_double(0x7ff8000000000000ll) : tc[zo + (long)r * P + c]) : 0.0;
   }
   __syncthreads();
   for (int k = ty; k < 32; k += 8) {
     // upper tile position (r, c): only elements on / above the diagonal are valid inputs
     int r = bi * 32 + k, c = bj * 32 + tx;
-    if (r < P && c < P && c >= r) denom[zo + (long)r * P + c] = tr[k][tx] + tt[k][tx];
+    if (r < P && c < P && c >= r) {
+      denom[zo + (long)r * P + c] = tr[k][tx] + tt[k][tx];
+      if (tc_nan && tc_nan[blockIdx.z]) tc[zo + (long)r * P + c] = tt[k][tx];
+    }
     // mirrored position (c', r') = (bj * 32 + k, bi * 32 + tx) takes the value of (bi * 32 + tx, bj * 32 + k)
     r = bj * 32 + k; c = bi * 32 + tx;
     if (r < P && c < P && r > c) {
@@ -634,9 +640,9 @@ int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11,
   return 0;
 }
 
-int sym_finish(int B, int P, double* risk, double* tc, double* denom, cudaStream_t s) {
+int sym_finish(int B, int P, double* risk, double* tc, double* denom, const int* tc_nan, cudaStream_t s) {
   const int nb = ceil_div(P, 32);
-  sym_finish_kernel<<<dim3(nb, nb, B), dim3(32, 8), 0, s>>>(P, risk, tc, denom);
+  sym_finish_kernel<<<dim3(nb, nb, B), dim3(32, 8), 0, s>>>(P, risk, tc, denom, tc_nan);
   PFML_CHECK_LAUNCH();
   return 0;
 }

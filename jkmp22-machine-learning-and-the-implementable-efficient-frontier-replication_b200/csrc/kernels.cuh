@@ -65,7 +65,7 @@ int chain_init(int B, int NP, const double* mt, const double* g1, long sg, doubl
 int emu_standardize_slices(const PanelView& pv, int B, int NP, int P, int tau0, int ntau, const int* date_t, const int* sel,
                            const int* nsel, const BatchVecs& v, int8_t* out, double* scale_out, int* err, cudaStream_t s);
 int add_mat(int B, long n_elem, const double* a, const double* b, double* out, cudaStream_t s);
-int sym_finish(int B, int P, double* risk, double* tc, double* denom, cudaStream_t s);
+int sym_finish(int B, int P, double* risk, double* tc, double* denom, const int* tc_nan /* [B] or null */, cudaStream_t s);
 int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11, const double* g0, long sg, double* wk, double* cbs,
               cudaStream_t s);
 int row_scale(int B, int rows, int cols, long ld, long stride, const double* in, const double* rsv, long srs, double* out,

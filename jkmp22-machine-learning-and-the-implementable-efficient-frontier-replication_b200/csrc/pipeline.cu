@@ -261,6 +261,7 @@ struct StepWs {
   int8_t *eAs, *eBs; double *esa, *esb; int *eex, *eerr;   // INT8-emulated GEMM operands (emu.cu)
   double* chain;                                            // B~_2 .. B~_{lb-1} of the chain (B~_1 sits in Ya)
   int8_t* eMs; double* esm;                                 // B-type slices of m~ (kept through the chain / term loop)
+  int* ezf;                                                 // per-date flag: omega_chg holds NaN (quirk Q8)
   int8_t* eSs; double* eSsb;                                // B-type slices of the signal slabs 2 .. lb+1 and their scales
   double *St, *Za, *Zb, *Nn, *Nl1, *OM, *BS, *OMC;
   double *risk_tmp, *tc_tmp;
@@ -306,7 +307,7 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.eAs = c.take<int8_t>(emu_a_slices_bytes(B, Pn, NP));
   w.eBs = c.take<int8_t>(emu_b_slices_bytes(B, NP, Pn));
   w.esa = c.take<double>((size_t)B * Pn); w.esb = c.take<double>((size_t)B * Pn);
-  w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64);
+  w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64); w.ezf = c.take<int>((size_t)B);
   w.chain = nt >= 5 ? c.take<double>((size_t)(nt - 4) * BNN) : nullptr;   // lb - 2 matrices
   w.eMs = c.take<int8_t>(emu_b_slices_bytes(B, NP, NP)); w.esm = c.take<double>((size_t)B * NP);
   w.eSs = nt >= 3 ? c.take<int8_t>((size_t)(nt - 2) * emu_b_slices_bytes(B, NP, P)) : nullptr;
@@ -453,8 +454,8 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     {
       ProfScope ps(T_HORNER, s);
       // N = S~_0 + m~ G_0 Z  (the A slices of m~ are still in place);  N_l1 = Z + B11 S~_{lb+1}
-      if (NP == 512) {                  // G_0 Z is only ever this product's B operand: the row scale rides in the slicing
-        PFML_TRY(emu_slice_nmajor512(Z, ldP, nP, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s, gv(0), sg));
+      if (NP <= 1024) {                 // G_0 Z is only ever this product's B operand: the row scale rides in the slicing
+        PFML_TRY(emu_slice_nmajor512(Z, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s, gv(0), sg));
       } else {
         double* ZG = w.Zb;
         PFML_TRY(row_scale(B, NP, P, ldP, nP, Z, gv(0), sg, ZG, ldP, nP, s));
@@ -583,7 +584,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     PFML_TRY(gemm(f, B, s));
     PFML_TRY(row_scale(B, NP, P, ldP, sStack, w.OM, w.v.dvl, NP, w.BS, ldP, sStack, s));
     // risk = [omega~; Y]' [gamma (ivol/lambda) omega~; gamma F Y]
-    const bool emu_pp = emu && NP == 512 && emu_shape_ok(P, P, NP);   // the one-pass transposed slicing is written for K = 512
+    const bool emu_pp = emu && NP <= 1024 && emu_shape_ok(P, P, NP);   // the one-pass transposed slicing holds K <= 1024 in registers
     if (emu_pp) {
       // factor part (K = KP) on the DMMA pipe, then the n-deep part on the INT8 tensor cores accumulates onto it;
       // symmetric: only the upper triangle is computed; sym_finish mirrors it and forms denom
@@ -593,18 +594,19 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       r.D = risk; r.ldd = P; r.sD = (long)P * P;
       r.M = P; r.N = P; r.K = KP; r.sym = 1;
       PFML_TRY(gemm(r, B, s));
-      PFML_TRY(emu_slice_nmajor512(w.OM, ldP, sStack, P, B, nullptr, nullptr, nullptr, w.eAs, w.esa, w.eerr, s));
-      PFML_TRY(emu_slice_nmajor512(w.BS, ldP, sStack, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s));
+      PFML_TRY(emu_slice_nmajor512(w.OM, ldP, sStack, NP, P, B, nullptr, nullptr, nullptr, w.eAs, w.esa, w.eerr, s));
+      PFML_TRY(emu_slice_nmajor512(w.BS, ldP, sStack, NP, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s));
       EmuExtra xr;
       xr.sym = true; xr.digits = xq.digits;
       PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 1.0, risk, P, (long)P * P, risk, P, (long)P * P, xr,
                           w.eerr, s));
       // tc = w omega~_chg' omega~_chg ; denom = risk + tc
-      PFML_TRY(emu_slice_nmajor512(w.OMC, ldP, nP, P, B, w.eBs, w.esb, w.eex, w.eAs, w.esa, w.eerr, s));
+      PFML_CUDA_OK(cudaMemsetAsync(w.ezf, 0, sizeof(int) * B, s));
+      PFML_TRY(emu_slice_nmajor512(w.OMC, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, w.eAs, w.esa, w.eerr, s, nullptr, 0, w.ezf));
       EmuExtra xt;
       xt.sym = true; xt.az = w.v.scal + 0; xt.s_az = NSCAL; xt.digits = xq.digits;
       PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, tc, P, (long)P * P, xt, w.eerr, s));
-      PFML_TRY(sym_finish(B, P, risk, tc, denom, s));        // denom = risk + tc; lower triangles = copies of the upper
+      PFML_TRY(sym_finish(B, P, risk, tc, denom, w.ezf, s));        // denom = risk + tc; lower triangles = copies of the upper
       if (status) {
         fold_emu_error_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, w.eerr, status);
         PFML_CHECK_LAUNCH();

@@ -129,6 +129,19 @@ def test_nan_growth_semantics_q8(dev, syn):
     assert relerr(g["risk"], o["risk"]) < TOL
 
 
+def test_nan_growth_semantics_q8_n500(dev, syn):
+    """The same at n = 500 (padded 512), where risk / tc run on the INT8 tensor cores: a NaN growth rate at date d is
+    not an error (status 0) and makes every element of tc and denom NaN, as in the reference's dense product."""
+    panel = syn.make_panel(N=500, T=14, p=16, seed=26)
+    panel.tr_ld0[13, 7] = np.nan
+    rff_x, vs = _panel_pre(panel)
+    g = dev.date_steps(panel, [13])[0]
+    o = O.date_step(panel, 13, rff_x, vs)
+    assert g["status"] == 0
+    assert np.isnan(o["tc"]).all() and np.isnan(g["tc"]).all() and np.isnan(g["denom"]).all()
+    assert relerr(g["risk"], o["risk"]) < TOL
+
+
 def test_rff_and_vol_scale(dev, syn):
     panel = syn.make_panel(N=90, T=14, p=64, seed=25, barra_missing=0.3, ragged=0.3)
     dp = dev.DevicePanel(panel)
