@@ -5,7 +5,8 @@ import numpy as np, torch
 PKG = "jkmp22-machine-learning-and-the-implementable-efficient-frontier-replication_b200"
 syn = importlib.import_module(PKG + ".synthetic"); dm = importlib.import_module(PKG + ".device")
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
-panel = syn.make_panel(N=3000, T=syn.LB + 2 + B, p=1024, seed=11, ragged=0.01)
+NS = int(sys.argv[2]) if len(sys.argv) > 2 else 3000
+panel = syn.make_panel(N=NS, T=syn.LB + 2 + B, p=1024, seed=11, ragged=0.01)
 months = [int(t) for t in panel.hot_months()]
 dp = dm.DevicePanel(panel); sel, n_sel, n_max, NP = dm.universe(panel, months)
 r = dm.DateStepRunner(dp, B, n_max); r.set_batch(months, sel, n_sel)
