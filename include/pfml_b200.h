@@ -11,12 +11,23 @@
  *     `_host`; index arrays are int32;
  *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are asynchronous on it;
  *   - no hidden allocation: the caller passes a workspace whose size the matching *_workspace_bytes query
- *     returns (the *_host convenience entry points allocate and free their own device buffers);
- *   - return value: 0 ok; <0 bad argument / CUDA error (text via pfml_last_error()); numerical failures are
- *     reported per date in the `status` array (bit 0: singular pivot in a block inverse, bit 1: matrix
- *     square root did not converge / non-finite input, bit 3: a barrier wait inside the INT8-emulated GEMM timed
- *     out, bit 4: NaN/Inf reached an operand of that GEMM);
- *   - never throws, never exits; thread-safe per stream.
+ *     returns.  Exception: the *_host convenience entry points keep one grow-only device arena per GPU (sized by
+ *     the largest call so far, reused by later calls, never freed before process exit) plus their own streams;
+ *   - return value: 0 ok; <0 bad argument / CUDA error (text via pfml_last_error(), per thread); numerical
+ *     failures are reported PER DATE in the `status` array:
+ *       bit 0 (1)   singular pivot in a block inverse,
+ *       bit 1 (2)   matrix square root did not converge / non-finite input of m_func,
+ *       bit 2 (4)   an eigenvalue of x = Sigma~ / w below 1e-8: outside the design range of the quadrature that
+ *                   replaces sqrtm (General_functions.py:956),
+ *       bit 3 (8)   a barrier wait inside the INT8-emulated GEMM timed out (kernel-wide: set on every date of the call),
+ *       bit 4 (16)  NaN / Inf reached an operand of that GEMM for THIS date: its r_tilde, denom, risk and tc are
+ *                   returned as NaN (what the reference's FP64 arithmetic yields), the other dates of the batch are
+ *                   unaffected and bit-identical to a batch without the bad date;
+ *   - never throws, never exits.  Threading: calls on different streams / devices may run concurrently from
+ *     different host threads; the launch counter, the emulation mode (read once at the start of each call) and the
+ *     one-time kernel configuration are atomic.  The *_host entry points serialise per GPU (one arena per GPU),
+ *     not across GPUs, and restore the caller's current device.  The profiling hooks (pfml_prof_*) are for a
+ *     single measuring thread.
  */
 #ifndef PFML_B200_H
 #define PFML_B200_H
@@ -74,6 +85,38 @@ size_t pfml_date_steps_workspace_bytes(const pfml_panel_t* panel, int B, int n_m
 int pfml_date_steps(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
                     double* r_tilde, double* denom, double* risk, double* tc, double* signal_t, int* status,
                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* a3..a9 + a11 -- the same date-steps with the expanding-window sums of PFML_Search_Coef.py:77-88, :112-121 fused in:
+ * bucket [B] (device int32) is the window of each date (0 = burn-in, k = k-th hp year, outside [0, n_buckets): none);
+ * r_sum [n_buckets][P] and d_sum [n_buckets][P][P] are ACCUMULATED into (zero them before the first call): every
+ * window receives the in-order (left-to-right, like the reference's reduce(+), :37-46) sum of its dates of this
+ * call.  On the INT8 path the sums of denom are formed in the a9 finish kernel that writes denom, so denom is not
+ * read again.  Partial sums of different ranks are then combined with pfml_comm_allreduce_sums. */
+int pfml_date_steps_bucketed(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                             const int* bucket, int n_buckets, double* r_sum, double* d_sum, double* r_tilde, double* denom,
+                             double* risk, double* tc, double* signal_t, int* status, void* workspace, size_t workspace_bytes,
+                             void* stream);
+
+/* Stage-level entry points: the same kernels as pfml_date_steps, stopped / started at a stage boundary, so that
+ * each stage can be called, parity-tested and profiled on its own.  All take the workspace of
+ * pfml_date_steps_workspace_bytes and the same date_t / sel / n_sel arrays; matrices are [B][NP][.] with rows
+ * >= n_sel[b] zero, columns in feat_all order.
+ *   pfml_standardize_scale     a6: signals[tau] = diag(1/vol_scale) s for tau = 0..lb+1 (PFML_Input_Data.py:357-388)
+ *                              -> signals [B][lb+2][NP][P]
+ *   pfml_omega_batched         a3..a8: omega = solve(const, sum A_theta S_theta), omega_chg = omega - G_0 omega_l1
+ *                              (PFML_Input_Data.py:400-462) -> omega, omega_chg [B][NP][P]; m (may be NULL) receives
+ *                              m_func's result [B][NP][NP] (General_functions.py:919-962)
+ *   pfml_rtilde_denom_batched  a9 from GIVEN omega / omega_chg [B][NP][P] (e.g. the oracle's): r_tilde = omega' r,
+ *                              risk = gamma omega' Sigma omega, tc = w omega_chg' Lambda omega_chg, denom = risk + tc
+ *                              (PFML_Input_Data.py:470-481); risk / tc may be NULL */
+int pfml_standardize_scale(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                           double* signals, void* workspace, size_t workspace_bytes, void* stream);
+int pfml_omega_batched(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                       double* omega, double* omega_chg, double* m, int* status, void* workspace, size_t workspace_bytes,
+                       void* stream);
+int pfml_rtilde_denom_batched(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                              const double* omega, const double* omega_chg, double* r_tilde, double* denom, double* risk,
+                              double* tc, int* status, void* workspace, size_t workspace_bytes, void* stream);
 
 /* a5 -- m_func(w, mu, rf, sigma_gam, gam, K_Lambda, iterations), General_functions.py:919-962, batched over
  * B problems of equal size n: sigma_gam [B][n][n], lam [B][n] (diagonal of K_Lambda), w [B], rf [B] -> m [B][n][n]. */

@@ -206,13 +206,7 @@ int pfml_backtest(const pfml_panel_t* panel, const double* me, const double* tr_
     return -2;
   }
   cudaStream_t s = (cudaStream_t)stream;
-  static bool cfg[64] = {};
-  int dev = 0;
-  PFML_CUDA_OK(cudaGetDevice(&dev));
-  if (!cfg[dev & 63]) {
-    PFML_CUDA_OK(cudaFuncSetAttribute(backtest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    cfg[dev & 63] = true;
-  }
+  PFML_CONFIG_ONCE(backtest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   backtest_kernel<<<1, 1024, smem, s>>>(B, NP, panel->N, m, w_aim, date_t, sel, n_sel, me, tr_ld1, mu_ld1, panel->ret_ld1,
                                         panel->lam, panel->wealth, carry, w_start, w, stats);
   PFML_CHECK_LAUNCH();

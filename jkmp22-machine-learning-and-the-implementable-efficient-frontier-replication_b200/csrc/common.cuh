@@ -1,8 +1,10 @@
 // Shared declarations for the PFML sm_100a kernels (internal; the public C ABI is include/pfml_b200.h).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
 
 namespace pfml {
 
@@ -19,15 +21,28 @@ const char* last_error();
     }                                                                                        \
   } while (0)
 
-extern long g_launch_count;   // kernels launched by this library (bench.py's gpu_launches)
+extern std::atomic<long> g_launch_count;   // kernels launched by this library (bench.py's gpu_launches)
 
 #define PFML_CHECK_LAUNCH()                                                                  \
   do {                                                                                       \
-    ++pfml::g_launch_count;                                                                  \
+    pfml::g_launch_count.fetch_add(1, std::memory_order_relaxed);                            \
     cudaError_t _e = cudaGetLastError();                                                     \
     if (_e != cudaSuccess) {                                                                 \
       pfml::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
       return -101;                                                                           \
+    }                                                                                        \
+  } while (0)
+
+// One-time (per device) kernel attribute.  cudaFuncSetAttribute is idempotent, so two threads racing through the first
+// call both set the same value; the flag itself is atomic.
+#define PFML_CONFIG_ONCE(kern, attr, value)                                                  \
+  do {                                                                                       \
+    static std::atomic<bool> _cfg[64];                                                       \
+    int _dev = 0;                                                                            \
+    PFML_CUDA_OK(cudaGetDevice(&_dev));                                                      \
+    if (!_cfg[_dev & 63].load(std::memory_order_acquire)) {                                  \
+      PFML_CUDA_OK(cudaFuncSetAttribute(kern, attr, value));                                 \
+      _cfg[_dev & 63].store(true, std::memory_order_release);                                \
     }                                                                                        \
   } while (0)
 
@@ -64,6 +79,11 @@ struct GemmP {
 
 int gemm(const GemmP& p, int batch, cudaStream_t stream);
 double gemm_flops(const GemmP& p, int batch);
+
+// Error words of the INT8 path (`err`, device int array of EMU_ERR_SLOT0 + batch entries, zeroed by the caller):
+//   err[0]                  bits 0-3: a barrier wait inside emu_gemm_kernel timed out (kernel-wide, not attributable to a matrix)
+//   err[EMU_ERR_SLOT0 + z]  bit 4: matrix z of the batch held NaN / Inf in an operand (it cannot be sliced)
+constexpr int EMU_ERR_SLOT0 = 64;
 
 // ---- FP64 GEMM emulated on the INT8 tensor cores (emu.cu): tcgen05.mma kind::i8 + TMEM + bulk-TMA staging ----------
 size_t emu_a_slices_bytes(int batch, int M, int K);

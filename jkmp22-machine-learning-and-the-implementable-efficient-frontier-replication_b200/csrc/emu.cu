@@ -53,7 +53,8 @@ __device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* ds
     const int ex = (int)((bits >> 52) & 0x7ff);
     const unsigned long long mant = ((unsigned long long)bits & 0xFFFFFFFFFFFFFull) | (ex ? (1ull << 52) : 0ull);
     const int sh = 1075 + e - (8 * ES - 2) - ex;           // |F| = round(mant 2^-sh)
-    const unsigned long long fv = (ex == 0 || sh >= 64) ? 0ull : (sh > 0 ? ((mant + (1ull << (sh - 1))) >> sh) : (mant << (-sh)));
+    // NaN / Inf (ex == 0x7ff) have no digits: they are flagged per matrix by the callers and sliced as zero (no shift >= 64)
+    const unsigned long long fv = (ex == 0 || ex == 0x7ff || sh >= 64 || sh <= -11) ? 0ull : (sh > 0 ? ((mant + (1ull << (sh - 1))) >> sh) : (mant << (-sh)));
     const unsigned long long g = ((unsigned long long)(bits < 0 ? -(long long)fv : (long long)fv) + Bz) ^ Bz;
     lo[k] = (unsigned)g; hi[k] = (unsigned)(g >> 32);
   }
@@ -93,7 +94,7 @@ __global__ void slice_kmajor_kernel(const double* __restrict__ X, long ld, long 
     bool bad = false;
     for (int k = lane; k < K; k += 32) { const double v = fabs(a[k]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
     for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (bad) atomicOr(err, 16);                  // NaN / Inf cannot be sliced: reported through the status array
+    if (bad) atomicOr(err + EMU_ERR_SLOT0 + z, 16);   // NaN / Inf cannot be sliced: reported per matrix through the status array
     e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
     if (lane == 0) scale[(long)z * R + row] = scalbn(extra, e);
   }
@@ -136,7 +137,7 @@ slice_kmajor512_kernel(const double* __restrict__ X, long ld, long sX, int R, in
       for (int k = 0; k < 16; k++) x[h][k] = 0.0;
     }
   }
-  if (bad) atomicOr(err, 16);
+  if (bad) atomicOr(err + EMU_ERR_SLOT0 + z, 16);
   mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
   mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
   if (c == 0) s_mx[w][r] = mx;
@@ -162,7 +163,7 @@ __global__ void col_exponent_kernel(const double* __restrict__ X, long ld, long 
   double mx = 0.0;
   bool bad = false;
   for (int k = 0; k < K; k++) { const double v = fabs(b[(long)k * ld]); bad |= !(v <= 1.7976931348623157e308); mx = fmax(mx, v); }
-  if (bad) atomicOr(err, 16);
+  if (bad) atomicOr(err + EMU_ERR_SLOT0 + z, 16);
   const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
   ex[(long)z * C + n] = e;
   scale[(long)z * C + n] = scalbn(extra, e);
@@ -214,7 +215,7 @@ slice_nmajor512_kernel(const double* __restrict__ X, long ld, long sX, int K, in
   }
   // a non-finite operand is an error (status bit 4) unless the caller asked for a per-matrix flag instead (zflag: the
   // reference's own NaN semantics, quirk Q8, are then reproduced by the caller)
-  if (bad) { if (zflag) atomicOr(zflag + z, 1); else atomicOr(err, 16); }
+  if (bad) { if (zflag) atomicOr(zflag + z, 1); else atomicOr(err + EMU_ERR_SLOT0 + z, 16); }
   red[kq][lane] = mx;
   __syncthreads();
   for (int j = 0; j < NKQ; j++) mx = fmax(mx, red[j][lane]);
@@ -312,7 +313,7 @@ standardize_slice_kernel(PanelView pv, int NP, int P, int tau0, const int* __res
     mx *= scale;                                                  // largest |value| up to rounding (digits tolerate 1.98 * 2^e)
     bad |= !(mx <= 1.7976931348623157e308);
   }
-  if (bad) atomicOr(err, 16);                               // NaN / Inf cannot be sliced: reported through the status array
+  if (bad) atomicOr(err + EMU_ERR_SLOT0 + b, 16);          // NaN / Inf cannot be sliced: reported per date through the status array
   const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
   if (real && rq == 0) scale_out[((long)blockIdx.y * gridDim.z + b) * P + j] = scalbn(kBScale, e);
   // pass 3: digits
@@ -409,7 +410,7 @@ standardize_slice512_kernel(PanelView pv, int NP, int P, int tau0, const int* __
   const double scale = real ? ((j == 0) ? sqrt(1.0 / (double)n) : sqrt(1.0 / ss)) : 0.0;
   mx *= scale;                                               // largest |value| up to rounding (digits tolerate 1.98 * 2^e)
   bad |= real && !(ss <= 1.7976931348623157e308 && mx <= 1.7976931348623157e308);
-  if (bad) atomicOr(err, 16);
+  if (bad) atomicOr(err + EMU_ERR_SLOT0 + b, 16);
   const int e = (mx > 0.0 && isfinite(mx)) ? ilogb(mx) + 1 : 0;
   if (real && rg == 0) scale_out[((long)blockIdx.y * nB + b) * P + j] = scalbn(kBScale, e);
   if (i0 >= NP || j / EBN >= CB) return;
@@ -808,16 +809,18 @@ int emu_mma_ex(const int8_t* As, const double* sa, const int8_t* Bs, const doubl
   }
   if (p.q > 8 * (digits - 1)) p.q = 8 * (digits - 1);
   constexpr size_t smem = (size_t)ESTAGES * (EA_STAGE + EB_STAGE) + (size_t)(4 * EPI_G) * 32 * 9 * sizeof(double);
-  static bool cfg[64] = {};
+  static std::once_flag once[64];
   static int n_sm[64] = {};
+  static cudaError_t cfg_rc[64] = {};
   int dev = 0;
   PFML_CUDA_OK(cudaGetDevice(&dev));
-  if (!cfg[dev & 63]) {
-    PFML_CUDA_OK(cudaFuncSetAttribute(emu_gemm_kernel<ES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    PFML_CUDA_OK(cudaFuncSetAttribute(emu_gemm_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    PFML_CUDA_OK(cudaDeviceGetAttribute(&n_sm[dev & 63], cudaDevAttrMultiProcessorCount, dev));
-    cfg[dev & 63] = true;
-  }
+  std::call_once(once[dev & 63], [&] {       // per device, safe under concurrent first calls
+    cudaError_t rc = cudaFuncSetAttribute(emu_gemm_kernel<ES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (rc == cudaSuccess) rc = cudaFuncSetAttribute(emu_gemm_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (rc == cudaSuccess) rc = cudaDeviceGetAttribute(&n_sm[dev & 63], cudaDevAttrMultiProcessorCount, dev);
+    cfg_rc[dev & 63] = rc;
+  });
+  PFML_CUDA_OK(cfg_rc[dev & 63]);
   const long tiles = (long)batch * p.MB * p.NB;
   const long want = n_sm[dev & 63];                       // persistent: one CTA per SM (it owns the SM's whole TMEM)
   const int grid = (int)(tiles < want ? tiles : want);

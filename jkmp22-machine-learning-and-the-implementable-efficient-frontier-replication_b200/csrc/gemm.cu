@@ -240,13 +240,7 @@ int launch(const GemmP& p, int batch, cudaStream_t stream) {
   constexpr int NT = (BM / WM) * (BN / WN) * 32;
   constexpr size_t smem = (size_t)STAGES * (TileSize<BM, BK, AKIN>::value + TileSize<BN, BK, BKIN>::value) * sizeof(double);
   auto kern = gemm_kernel<BM, BN, WM, WN, BK, STAGES, MINB, AKIN, BKIN, VEC>;
-  static bool configured[64] = {};   // per instantiation and device; the attribute is per-function per-context
-  int dev = 0;
-  PFML_CUDA_OK(cudaGetDevice(&dev));
-  if (!configured[dev & 63]) {
-    PFML_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured[dev & 63] = true;
-  }
+  PFML_CONFIG_ONCE(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per instantiation and device
   dim3 grid(ceil_div(p.N, BN), ceil_div(p.M, BM), batch);
   kern<<<grid, NT, smem, stream>>>(p);
   PFML_CHECK_LAUNCH();

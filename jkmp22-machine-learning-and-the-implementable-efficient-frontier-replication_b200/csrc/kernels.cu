@@ -151,7 +151,8 @@ __global__ void build_x_dense_kernel(int n, int NP, const double* __restrict__ s
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 standardize_kernel(PanelView pv, int NP, int P, long ldP, const int* __restrict__ date_t, const int* __restrict__ sel,
-                   const int* __restrict__ nsel, BatchVecs v, double* __restrict__ St, double* __restrict__ signal_t, int prescale) {
+                   const int* __restrict__ nsel, BatchVecs v, double* __restrict__ St, double* __restrict__ signal_t, int prescale,
+                   double* __restrict__ signals_all) {
   const int b = blockIdx.z, tau = blockIdx.y;
   const int j = blockIdx.x * blockDim.x + threadIdx.x;   // output column (0 = constant)
   const int n = nsel[b], t = date_t[b] - tau;
@@ -181,7 +182,9 @@ standardize_kernel(PanelView pv, int NP, int P, long ldP, const int* __restrict_
   const double* __restrict__ slb = v.sl + (long)b * NP;
   const double* __restrict__ gprev = (prescale && tau >= 2 && tau <= pv.lb) ? v.g + ((long)b * nt + (tau - 1)) * NP : nullptr;
   double* __restrict__ out = St + (((long)b * nt + tau) * NP) * ldP + j;
-  double* __restrict__ sig = (tau == 0 && signal_t) ? signal_t + (long)b * NP * P + j : nullptr;
+  // signal_t: slab 0 only (what the reference stores, :485-489); signals_all: every slab [B][lb+2][NP][P] (stage entry point)
+  double* __restrict__ sig = signals_all ? signals_all + (((long)b * nt + tau) * NP) * P + j
+                                         : ((tau == 0 && signal_t) ? signal_t + (long)b * NP * P + j : nullptr);
 #pragma unroll 4
   for (int i = 0; i < n; i++) {
     const int s = s_sel[i];
@@ -232,39 +235,98 @@ __global__ void chain_sum_kernel(int NP, int nk, ChainPtrs p, const double* __re
 }
 
 // a9 finish for the upper-triangle products: denom = risk + tc, and risk, tc, denom mirrored into their lower triangles
-// (32 x 32 tiles through shared memory so that both the reads and the transposed writes are coalesced)
-__global__ void sym_finish_kernel(int P, double* __restrict__ risk, double* __restrict__ tc, double* __restrict__ denom,
-                                  const int* __restrict__ tc_nan) {
+// (32 x 32 tiles through shared memory so that both the reads and the transposed writes are coalesced).
+//   tc_nan[date]    omega_chg held NaN (quirk Q8: missing growth rate at date d): every element of tc and denom is NaN, as
+//                   in the reference's dense product
+//   bad[date] & 16  an operand of the INT8 products of this date held NaN / Inf (it was sliced as zero): risk, tc and denom
+//                   are all NaN, which is what the reference's FP64 arithmetic returns for such a date
+// With `bucket` (expanding-window sums of PFML_Search_Coef.py:77-88, :112-121 fused in): blockIdx.z is a window k, the
+// block walks the dates of that window in order and adds their in-order sum of denom to d_sum[k] (z = n_buckets takes the
+// dates that belong to no window).  Without it blockIdx.z is the date.
+__device__ __forceinline__ double qnan() { return __longlong_as_double(0x7ff8000000000000ll); }
+
+template <bool BUCKETS>
+__global__ void sym_finish_kernel(int B, int P, double* __restrict__ risk, double* __restrict__ tc, double* __restrict__ denom,
+                                  const int* __restrict__ tc_nan, const int* __restrict__ bad, const int* __restrict__ bucket,
+                                  int n_buckets, double* __restrict__ d_sum) {
   __shared__ double tr[32][33], tt[32][33];
   const int bi = blockIdx.y, bj = blockIdx.x;
   if (bj < bi) return;
-  const long zo = (long)blockIdx.z * P * P;
   const int tx = threadIdx.x, ty = threadIdx.y;
-  for (int k = ty; k < 32; k += 8) {
-    const int r = bi * 32 + k, c = bj * 32 + tx;
-    const bool ok = r < P && c < P;
-    tr[k][tx] = ok ? risk[zo + (long)r * P + c] : 0.0;
-    // tc_nan[date]: omega_chg held NaN (quirk Q8: missing growth rate at date d) -> every element of tc is NaN, as in
-    // the reference's dense product
-    tt[k][tx] = ok ? ((tc_nan && tc_nan[blockIdx.z]) ? __longlong_as_double(0x7ff8000000000000ll) : tc[zo + (long)r * P + c]) : 0.0;
-  }
-  __syncthreads();
-  for (int k = ty; k < 32; k += 8) {
-    // upper tile position (r, c): only elements on / above the diagonal are valid inputs
-    int r = bi * 32 + k, c = bj * 32 + tx;
-    if (r < P && c < P && c >= r) {
-      denom[zo + (long)r * P + c] = tr[k][tx] + tt[k][tx];
-      if (tc_nan && tc_nan[blockIdx.z]) tc[zo + (long)r * P + c] = tt[k][tx];
+  double acc_u[4], acc_l[4];
+  bool any = false;
+  const int b_lo = BUCKETS ? 0 : blockIdx.z, b_hi = BUCKETS ? B : blockIdx.z + 1;
+  for (int b = b_lo; b < b_hi; b++) {
+    if (BUCKETS) {
+      const int kb = bucket[b];
+      if (((kb >= 0 && kb < n_buckets) ? kb : n_buckets) != (int)blockIdx.z) continue;     // uniform over the block
     }
-    // mirrored position (c', r') = (bj * 32 + k, bi * 32 + tx) takes the value of (bi * 32 + tx, bj * 32 + k)
-    r = bj * 32 + k; c = bi * 32 + tx;
-    if (r < P && c < P && r > c) {
-      const double rv = tr[tx][k], tv = tt[tx][k];
-      risk[zo + (long)r * P + c] = rv;
-      tc[zo + (long)r * P + c] = tv;
-      denom[zo + (long)r * P + c] = rv + tv;
+    const long zo = (long)b * P * P;
+    const bool all_nan = bad && (bad[b] & 16), t_nan = all_nan || (tc_nan && tc_nan[b]);
+    for (int k = ty; k < 32; k += 8) {
+      const int r = bi * 32 + k, c = bj * 32 + tx;
+      const bool ok = r < P && c < P;
+      tr[k][tx] = ok ? (all_nan ? qnan() : risk[zo + (long)r * P + c]) : 0.0;
+      tt[k][tx] = ok ? (t_nan ? qnan() : tc[zo + (long)r * P + c]) : 0.0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const int k = ty + 8 * q;
+      // upper tile position (r, c): only elements on / above the diagonal are valid inputs
+      int r = bi * 32 + k, c = bj * 32 + tx;
+      if (r < P && c < P && c >= r) {
+        const double d = tr[k][tx] + tt[k][tx];
+        denom[zo + (long)r * P + c] = d;
+        if (t_nan) tc[zo + (long)r * P + c] = tt[k][tx];
+        if (all_nan) risk[zo + (long)r * P + c] = tr[k][tx];
+        if (BUCKETS) acc_u[q] = any ? acc_u[q] + d : d;
+      }
+      // mirrored position (c', r') = (bj * 32 + k, bi * 32 + tx) takes the value of (bi * 32 + tx, bj * 32 + k)
+      r = bj * 32 + k; c = bi * 32 + tx;
+      if (r < P && c < P && r > c) {
+        const double rv = tr[tx][k], tv = tt[tx][k];
+        risk[zo + (long)r * P + c] = rv;
+        tc[zo + (long)r * P + c] = tv;
+        denom[zo + (long)r * P + c] = rv + tv;
+        if (BUCKETS) acc_l[q] = any ? acc_l[q] + (rv + tv) : (rv + tv);
+      }
+    }
+    any = true;
+    if (BUCKETS) __syncthreads();
+  }
+  if (BUCKETS && any && (int)blockIdx.z < n_buckets) {
+    double* out = d_sum + (long)blockIdx.z * P * P;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const int k = ty + 8 * q;
+      int r = bi * 32 + k, c = bj * 32 + tx;
+      if (r < P && c < P && c >= r) out[(long)r * P + c] += acc_u[q];
+      r = bj * 32 + k; c = bi * 32 + tx;
+      if (r < P && c < P && r > c) out[(long)r * P + c] += acc_l[q];
     }
   }
+}
+
+// r_tilde (and, off the symmetric INT8 path, the matrices) of a date whose operands held NaN / Inf -> NaN
+__global__ void poison_kernel(int P, const int* __restrict__ bad, double* __restrict__ r_tilde, double* __restrict__ denom,
+                              double* __restrict__ risk, double* __restrict__ tc) {
+  const int b = blockIdx.x;
+  if (!(bad[b] & 16)) return;
+  for (int j = threadIdx.x; j < P; j += blockDim.x) r_tilde[(long)b * P + j] = qnan();
+  for (long e = threadIdx.x; e < (long)P * P; e += blockDim.x) {
+    if (denom) denom[(long)b * P * P + e] = qnan();
+    if (risk) risk[(long)b * P * P + e] = qnan();
+    if (tc) tc[(long)b * P * P + e] = qnan();
+  }
+}
+
+// omega~ = Lambda^1/2 omega for rows < n, zero rows beyond (stage entry: a9 from a given omega)
+__global__ void tilde_rows_kernel(int NP, int P, const double* __restrict__ in, const int* __restrict__ nsel, const double* __restrict__ sl,
+                                  double* __restrict__ out, long ldo, long stride_o) {
+  const int b = blockIdx.z, i = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= P) return;
+  out[(long)b * stride_o + (long)i * ldo + j] = i < nsel[b] ? sl[(long)b * NP + i] * in[((long)b * NP + i) * P + j] : 0.0;
 }
 
 // partial Frobenius sums of M, Mi and M - I over a chunk of rows; deterministic two-stage reduction
@@ -615,9 +677,9 @@ int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* l
 }
 
 int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
-                const BatchVecs& v, double* St, double* signal_t, bool prescale, int ntau, cudaStream_t s) {
+                const BatchVecs& v, double* St, double* signal_t, bool prescale, int ntau, cudaStream_t s, double* signals_all) {
   dim3 grid(ceil_div(P, 128), ntau, B);
-  standardize_kernel<<<grid, 128, NP * sizeof(int), s>>>(pv, NP, P, ldP, date_t, sel, nsel, v, St, signal_t, prescale ? 1 : 0);
+  standardize_kernel<<<grid, 128, NP * sizeof(int), s>>>(pv, NP, P, ldP, date_t, sel, nsel, v, St, signal_t, prescale ? 1 : 0, signals_all);
   PFML_CHECK_LAUNCH();
   return 0;
 }
@@ -640,9 +702,26 @@ int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11,
   return 0;
 }
 
-int sym_finish(int B, int P, double* risk, double* tc, double* denom, const int* tc_nan, cudaStream_t s) {
+int sym_finish(int B, int P, double* risk, double* tc, double* denom, const int* tc_nan, const int* bad, const int* bucket,
+               int n_buckets, double* d_sum, cudaStream_t s) {
   const int nb = ceil_div(P, 32);
-  sym_finish_kernel<<<dim3(nb, nb, B), dim3(32, 8), 0, s>>>(P, risk, tc, denom, tc_nan);
+  if (bucket && d_sum && n_buckets > 0)
+    sym_finish_kernel<true><<<dim3(nb, nb, n_buckets + 1), dim3(32, 8), 0, s>>>(B, P, risk, tc, denom, tc_nan, bad, bucket, n_buckets, d_sum);
+  else
+    sym_finish_kernel<false><<<dim3(nb, nb, B), dim3(32, 8), 0, s>>>(B, P, risk, tc, denom, tc_nan, bad, nullptr, 0, nullptr);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int poison_bad_dates(int B, int P, const int* bad, double* r_tilde, double* denom, double* risk, double* tc, cudaStream_t s) {
+  poison_kernel<<<B, 256, 0, s>>>(P, bad, r_tilde, denom, risk, tc);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+
+int tilde_rows(int B, int NP, int P, const double* in, const int* nsel, const double* sl, double* out, long ldo, long stride_o,
+               cudaStream_t s) {
+  tilde_rows_kernel<<<grid_rc(P, NP, B), 128, 0, s>>>(NP, P, in, nsel, sl, out, ldo, stride_o);
   PFML_CHECK_LAUNCH();
   return 0;
 }
@@ -740,13 +819,7 @@ int vol_scale_panel(const double* fct_load, const double* fct_cov, const double*
       return -2;
     }
     size_t smem = (size_t)npow * sizeof(double);
-    static bool cfg[64] = {};
-    int dev = 0;
-    PFML_CUDA_OK(cudaGetDevice(&dev));
-    if (!cfg[dev & 63]) {
-      PFML_CUDA_OK(cudaFuncSetAttribute(median_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8));
-      cfg[dev & 63] = true;
-    }
+    PFML_CONFIG_ONCE(median_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8);
     median_fill_kernel<<<T, 512, smem, s>>>(N, npow, vol_scale);
     PFML_CHECK_LAUNCH();
   }

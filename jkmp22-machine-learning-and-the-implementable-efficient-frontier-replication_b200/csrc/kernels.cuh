@@ -53,7 +53,8 @@ int build_x_dense(int B, int n, int NP, const double* sigma_gam, const double* l
 
 int standardize(const PanelView& pv, int B, int NP, int P, long ldP, const int* date_t, const int* sel, const int* nsel,
                 const BatchVecs& v, double* St /*[B][lb+2][NP][ldP]*/, double* signal_t /*[B][NP][P] or null*/, bool prescale /* g_{tau-1} row scale for tau in 2..lb */,
-                int ntau /* slabs 0 .. ntau-1 are written */, cudaStream_t s);
+                int ntau /* slabs 0 .. ntau-1 are written */, cudaStream_t s,
+                double* signals_all = nullptr /* [B][lb+2][NP][P]: diag(1/vol) s of every slab, un-tilded */);
 
 // n x n helpers on [B][NP][NP] buffers
 int copy2(int B, long n_elem, const double* src, double* d1, double* d2, cudaStream_t s);
@@ -65,7 +66,14 @@ int chain_init(int B, int NP, const double* mt, const double* g1, long sg, doubl
 int emu_standardize_slices(const PanelView& pv, int B, int NP, int P, int tau0, int ntau, const int* date_t, const int* sel,
                            const int* nsel, const BatchVecs& v, int8_t* out, double* scale_out, int* err, cudaStream_t s);
 int add_mat(int B, long n_elem, const double* a, const double* b, double* out, cudaStream_t s);
-int sym_finish(int B, int P, double* risk, double* tc, double* denom, const int* tc_nan /* [B] or null */, cudaStream_t s);
+// a9 finish (mirror, denom = risk + tc, NaN semantics); with `bucket` the per-window sums of denom are accumulated into d_sum
+int sym_finish(int B, int P, double* risk, double* tc, double* denom, const int* tc_nan /* [B] or null */, const int* bad /* [B] or null */,
+               const int* bucket /* [B] or null */, int n_buckets, double* d_sum /* [n_buckets][P][P] */, cudaStream_t s);
+int poison_bad_dates(int B, int P, const int* bad, double* r_tilde, double* denom, double* risk, double* tc, cudaStream_t s);
+int tilde_rows(int B, int NP, int P, const double* in, const int* nsel, const double* sl, double* out, long ldo, long stride_o,
+               cudaStream_t s);
+// out[bucket[b]] += in-order sum of in[b] (ridge.cu; PFML_Search_Coef.py:77-88, :112-121)
+int bucket_accumulate(int B, long elems, const double* in, const int* bucket, int n_buckets, double* out, cudaStream_t s);
 int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11, const double* g0, long sg, double* wk, double* cbs,
               cudaStream_t s);
 int row_scale(int B, int rows, int cols, long ld, long stride, const double* in, const double* rsv, long srs, double* out,

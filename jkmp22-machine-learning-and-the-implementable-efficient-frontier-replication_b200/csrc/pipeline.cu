@@ -27,7 +27,7 @@ namespace pfml {
 // ------------------------------------------------------------------------------------------------
 // errors, launch counter, profiling
 // ------------------------------------------------------------------------------------------------
-long g_launch_count = 0;
+std::atomic<long> g_launch_count{0};
 static thread_local char g_err[1024] = "";
 
 void set_error(const char* fmt, ...) {
@@ -58,7 +58,7 @@ static int slot_of(int tag) {
   }
 }
 struct ProfRec { int slot; cudaEvent_t e0, e1; double flops; };
-static bool g_prof_on = false;
+static std::atomic<bool> g_prof_on{false};
 static std::vector<ProfRec> g_recs;
 static std::vector<cudaEvent_t> g_open[N_TAGS];
 static std::mutex g_prof_mu;
@@ -183,20 +183,27 @@ int spd_inverse(int B, int NP, double* Wk, double* X, double* T1, int* status, c
 constexpr int DB_ITERS = 10;
 
 // n x n x P products of the date-step on the INT8 tensor cores (emu.cu) instead of the DMMA pipe
-static int g_use_emu = -1;
-static bool use_emu() {
-  if (g_use_emu < 0) {
+// The mode is process-wide but read ONCE per call (a call in flight keeps the mode it started with).
+static std::atomic<int> g_use_emu{-1};
+static int emu_mode() {
+  int m = g_use_emu.load(std::memory_order_relaxed);
+  if (m < 0) {
     const char* e = getenv("PFML_EMULATE_FP64");
-    g_use_emu = e ? atoi(e) : 1;
-    if (g_use_emu < 0 || g_use_emu > 2) g_use_emu = 1;
+    m = e ? atoi(e) : 1;
+    if (m < 0 || m > 2) m = 1;
+    g_use_emu.store(m, std::memory_order_relaxed);
   }
-  return g_use_emu != 0;
+  return m;
 }
 
-__global__ void fold_emu_error_kernel(int B, const int* __restrict__ err, int* __restrict__ status) {
+// err[0] bits 0-3: a barrier wait of the INT8 GEMM timed out (any matrix may be affected: status bit 3 on every date);
+// err[EMU_ERR_SLOT0 + b] bit 4: NaN / Inf reached an operand of date / matrix b (status bit 4 on that date only).
+// single != 0: one status word for the whole batch (pfml_dgemm_emulated).
+__global__ void fold_emu_error_kernel(int B, const int* __restrict__ err, int* __restrict__ status, int single) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  const int e = *err;                      // bits 0-3: a barrier wait of the INT8 GEMM timed out; bit 4: NaN/Inf operand
-  if (b < B && e) atomicOr(status + b, ((e & 15) ? 8 : 0) | (e & 16));
+  if (b >= B) return;
+  const int e = ((err[0] & 15) ? 8 : 0) | (err[EMU_ERR_SLOT0 + b] & 16);
+  if (e) atomicOr(status + (single ? 0 : b), e);
 }
 
 struct MtBufs {
@@ -307,7 +314,7 @@ static StepWs carve_step(void* ws, size_t cap, int B, int NP, int P, int nt, int
   w.eAs = c.take<int8_t>(emu_a_slices_bytes(B, Pn, NP));
   w.eBs = c.take<int8_t>(emu_b_slices_bytes(B, NP, Pn));
   w.esa = c.take<double>((size_t)B * Pn); w.esb = c.take<double>((size_t)B * Pn);
-  w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(64); w.ezf = c.take<int>((size_t)B);
+  w.eex = c.take<int>((size_t)B * Pn); w.eerr = c.take<int>(EMU_ERR_SLOT0 + (size_t)B); w.ezf = c.take<int>((size_t)B);
   w.chain = nt >= 5 ? c.take<double>((size_t)(nt - 4) * BNN) : nullptr;   // lb - 2 matrices
   w.eMs = c.take<int8_t>(emu_b_slices_bytes(B, NP, NP)); w.esm = c.take<double>((size_t)B * NP);
   w.eSs = nt >= 3 ? c.take<int8_t>((size_t)(nt - 2) * emu_b_slices_bytes(B, NP, P)) : nullptr;
@@ -327,10 +334,20 @@ static PanelView view_of(const pfml_panel_t* p) {
   return v;
 }
 
+// Optional parts of a date-step call: the fused expanding-window sums and the stage taps / injections behind the
+// stage-level entry points (pfml_omega_batched, pfml_rtilde_denom_batched).
+struct StepOpts {
+  const int* bucket = nullptr; int n_buckets = 0; double* r_sum = nullptr; double* d_sum = nullptr;
+  double *omega_out = nullptr, *omega_chg_out = nullptr, *m_out = nullptr;    // un-tilded, [B][NP][P] / [B][NP][NP]
+  const double *omega_in = nullptr, *omega_chg_in = nullptr;                  // a9 from a given omega / omega_chg [B][NP][P]
+  bool stop_after_omega = false;
+};
+
 static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
                            double* r_tilde, double* denom, double* risk, double* tc, double* signal_t, int* status,
-                           void* workspace, size_t workspace_bytes, cudaStream_t s) {
-  if (!panel || B <= 0 || n_max <= 0 || !date_t || !sel || !n_sel || !r_tilde || !denom || !workspace) {
+                           void* workspace, size_t workspace_bytes, cudaStream_t s, const StepOpts& opt = StepOpts()) {
+  if (!panel || B <= 0 || n_max <= 0 || !date_t || !sel || !n_sel || !workspace ||
+      (!opt.stop_after_omega && (!r_tilde || !denom))) {
     set_error("pfml_date_steps: null/empty argument");
     return -1;
   }
@@ -364,39 +381,21 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   auto gv = [&](int tau) { return w.v.g + (long)tau * NP; };        // + b * nt * NP per batch
   const long sg = (long)nt * NP;
 
-  // ---- a5 m_tilde: m~_0 by quadrature + Woodbury (stieltjes.cu), then the fixed-point inverses -----
-  double* mt = nullptr;
-  {
-    ProfScope ps(T_MFUNC, s);
-    PFML_TRY(build_x_factor(pv, B, NP, date_t, sel, n_sel, w.v, w.m.x, w.m.sgr, w.m.yv, s));
-    PFML_TRY(mt0_stieltjes(B, NP, pv.K, n_sel, w.v, w.Ut, w.Ev, w.G, w.m.mt, status, s));
-    PFML_TRY(fixed_point(B, NP, pv.iterations, w.m, status, s, &mt));
-  }
-  const bool emu = use_emu() && emu_shape_ok(NP, P, NP);
+  const int mode = emu_mode();
+  const bool emu = mode != 0 && emu_shape_ok(NP, P, NP);
   const bool emu_nn = emu && emu_shape_ok(NP, NP, NP);
-
+  int* const bad = w.eerr + EMU_ERR_SLOT0;                 // per-date non-finite flags of the INT8 path
+  if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int) * (EMU_ERR_SLOT0 + (size_t)B), s));
   // direct form of the n x P sums (INT8 path): Z = sum_k B~_k S~_{k+1} term by term next to the chain products
   const bool direct = emu_nn && lb - 1 <= 16 && w.chain != nullptr;
   // mode 2 (direct form only): the products whose errors do not compound (n x P sums, solves, a9) use 6 of the 7
   // digits (21 products); the chain products, whose results are multiplied on, always use all 7
   EmuExtra xq;
-  xq.digits = (g_use_emu == 2 && direct) ? 6 : 0;
+  xq.digits = (mode == 2 && direct) ? 6 : 0;
   const double* emu_a_cur = nullptr;       // whose slices currently sit in w.eAs
-  if (emu) PFML_CUDA_OK(cudaMemsetAsync(w.eerr, 0, sizeof(int), s));
-  // ---- a6 standardise (after m~: the signal slabs reuse the quadrature stack's memory) -------------
-  {
-    ProfScope ps(T_STD, s);
-    // direct form: only S~_0 and S~_1 are needed in FP64 (addends); the other slabs go straight to INT8 digits
-    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, !direct, direct ? 2 : nt, s));
-    if (direct) PFML_TRY(emu_standardize_slices(pv, B, NP, P, 2, lb, date_t, sel, n_sel, w.v, w.eSs, w.eSsb, w.eerr, s));
-  }
-  // free n x n buffers after m_tilde: x, sgr, Mdb, Ya, Yb, Wk, T1 and whichever of {mt, Xinv} is not `mt`
-  double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
-  double* spare = (mt == w.m.mt) ? w.m.Xinv : w.m.mt;
-
-  // one n x n x P product D = alpha * rs o (A X) + E on whichever tensor pipe is selected; A is sliced on demand
   auto nxP = [&](const double* A, const double* X, long sX, double alpha, const double* rs, long s_rs, const double* E, long sE,
                  double* D, long sD) -> int {
+    // one n x n x P product D = alpha * rs o (A X) + E on whichever tensor pipe is selected; A is sliced on demand
     if (emu) {
       if (emu_a_cur != A) {
         PFML_TRY(emu_slice_a(A, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
@@ -411,6 +410,33 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     if (E) { g.E = E; g.lde = ldP; g.sE = sE; g.beta = 1.0; }
     return gemm(g, B, s);
   };
+  if (opt.omega_in) {
+    // ---- stage entry: a9 from a given omega / omega_chg (un-tilded): omega~ = Lambda^1/2 omega ----------
+    if (!opt.omega_chg_in) { set_error("pfml_rtilde_denom_batched: omega_chg missing"); return -1; }
+    PFML_TRY(tilde_rows(B, NP, P, opt.omega_in, n_sel, w.v.sl, w.OM, ldP, sStack, s));
+    PFML_TRY(tilde_rows(B, NP, P, opt.omega_chg_in, n_sel, w.v.sl, w.OMC, ldP, nP, s));
+  } else {
+  // ---- a5 m_tilde: m~_0 by quadrature + Woodbury (stieltjes.cu), then the fixed-point inverses -----
+  double* mt = nullptr;
+  {
+    ProfScope ps(T_MFUNC, s);
+    PFML_TRY(build_x_factor(pv, B, NP, date_t, sel, n_sel, w.v, w.m.x, w.m.sgr, w.m.yv, s));
+    PFML_TRY(mt0_stieltjes(B, NP, pv.K, n_sel, w.v, w.Ut, w.Ev, w.G, w.m.mt, status, s));
+    PFML_TRY(fixed_point(B, NP, pv.iterations, w.m, status, s, &mt));
+  }
+  if (opt.m_out) PFML_TRY(m_from_mtilde(B, NP, NP, mt, w.v.isl, w.v.sl, opt.m_out, s));
+
+  // ---- a6 standardise (after m~: the signal slabs reuse the quadrature stack's memory) -------------
+  {
+    ProfScope ps(T_STD, s);
+    // direct form: only S~_0 and S~_1 are needed in FP64 (addends); the other slabs go straight to INT8 digits
+    PFML_TRY(standardize(pv, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, signal_t, !direct, direct ? 2 : nt, s));
+    if (direct) PFML_TRY(emu_standardize_slices(pv, B, NP, P, 2, lb, date_t, sel, n_sel, w.v, w.eSs, w.eSsb, w.eerr, s));
+  }
+  // free n x n buffers after m_tilde: x, sgr, Mdb, Ya, Yb, Wk, T1 and whichever of {mt, Xinv} is not `mt`
+  double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
+  double* spare = (mt == w.m.mt) ? w.m.Xinv : w.m.mt;
+
   double* Z = nullptr;
   const size_t slabS = emu_b_slices_bytes(B, NP, P);
   if (direct) {
@@ -558,15 +584,23 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     PFML_TRY(nxP(w.XC, w.Nn, nP, 1.0, nullptr, 0, nullptr, 0, w.OM, sStack));
     // omega~_chg = omega~ - g0raw o (const_l1^-1 N_l1)   (quirk Q8: g0 without NaN->1)
     PFML_TRY(nxP(w.XCl1, w.Nl1, nP, -1.0, w.v.g0raw, NP, w.OM, sStack, w.OMC, nP));
+  }
+  }   // !omega_in
+  // stage taps: omega = Lambda^-1/2 omega~ (PFML_Input_Data.py:455), omega_chg (:459)
+  if (opt.omega_out) PFML_TRY(row_scale(B, NP, P, ldP, sStack, w.OM, w.v.isl, NP, opt.omega_out, P, (long)NP * P, s));
+  if (opt.omega_chg_out) PFML_TRY(row_scale(B, NP, P, ldP, nP, w.OMC, w.v.isl, NP, opt.omega_chg_out, P, (long)NP * P, s));
+  if (opt.stop_after_omega) {
     if (emu && status) {
-      fold_emu_error_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, w.eerr, status);
+      fold_emu_error_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, w.eerr, status, 0);
       PFML_CHECK_LAUNCH();
     }
+    return 0;
   }
 
   // ---- a9 r_tilde, risk, tc, denom ----------------------------------------------------------------
   {
     ProfScope ps(T_DENOM, s);
+    bool fused_sums = false;
     PFML_TRY(gemv_t(B, NP, P, w.OM, ldP, sStack, w.v.rv, NP, r_tilde, P, s));
     // Y = (L^-1/2 Lf)' omega~  -> rows NP.. of the OM stack
     GemmP y;
@@ -606,11 +640,10 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       EmuExtra xt;
       xt.sym = true; xt.az = w.v.scal + 0; xt.s_az = NSCAL; xt.digits = xq.digits;
       PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, tc, P, (long)P * P, xt, w.eerr, s));
-      PFML_TRY(sym_finish(B, P, risk, tc, denom, w.ezf, s));        // denom = risk + tc; lower triangles = copies of the upper
-      if (status) {
-        fold_emu_error_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, w.eerr, status);
-        PFML_CHECK_LAUNCH();
-      }
+      // denom = risk + tc; lower triangles = copies of the upper; the per-window sums of denom ride along
+      PFML_TRY(sym_finish(B, P, risk, tc, denom, w.ezf, bad, opt.bucket, opt.n_buckets, opt.d_sum, s));
+      PFML_TRY(poison_bad_dates(B, P, bad, r_tilde, nullptr, nullptr, nullptr, s));
+      fused_sums = true;
     } else {
     GemmP r;
     r.a_kinner = false; r.A = w.OM; r.lda = ldP; r.sA = sStack;
@@ -627,6 +660,16 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     t.az = w.v.scal + 0; t.s_z = NSCAL;
     t.M = P; t.N = P; t.K = NP; t.sym = 1;
     PFML_TRY(gemm(t, B, s));
+    if (emu) PFML_TRY(poison_bad_dates(B, P, bad, r_tilde, denom, risk, tc, s));
+    }
+    if (emu && status) {
+      fold_emu_error_kernel<<<ceil_div(B, 128), 128, 0, s>>>(B, w.eerr, status, 0);
+      PFML_CHECK_LAUNCH();
+    }
+    // ---- a11 expanding-window sums (PFML_Search_Coef.py:77-88, :112-121) of this batch, accumulated into r_sum / d_sum ----
+    if (opt.bucket && opt.n_buckets > 0) {
+      if (opt.r_sum) PFML_TRY(bucket_accumulate(B, P, r_tilde, opt.bucket, opt.n_buckets, opt.r_sum, s));
+      if (opt.d_sum && !fused_sums) PFML_TRY(bucket_accumulate(B, (long)P * P, denom, opt.bucket, opt.n_buckets, opt.d_sum, s));
     }
   }
   return 0;
@@ -719,6 +762,71 @@ int pfml_date_steps(const pfml_panel_t* panel, int B, int n_max, const int* date
                          workspace_bytes, (cudaStream_t)stream);
 }
 
+int pfml_date_steps_bucketed(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                             const int* bucket, int n_buckets, double* r_sum, double* d_sum, double* r_tilde, double* denom,
+                             double* risk, double* tc, double* signal_t, int* status, void* workspace, size_t workspace_bytes,
+                             void* stream) {
+  if (!bucket || n_buckets <= 0 || !r_sum || !d_sum) {
+    set_error("pfml_date_steps_bucketed: null/empty window arguments");
+    return -1;
+  }
+  StepOpts o;
+  o.bucket = bucket; o.n_buckets = n_buckets; o.r_sum = r_sum; o.d_sum = d_sum;
+  return date_steps_impl(panel, B, n_max, date_t, sel, n_sel, r_tilde, denom, risk, tc, signal_t, status, workspace, workspace_bytes,
+                         (cudaStream_t)stream, o);
+}
+
+// ---- stage-level entry points: a6, a3..a8, a9 on their own -----------------------------------------
+int pfml_standardize_scale(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                           double* signals, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!panel || B <= 0 || n_max <= 0 || !date_t || !sel || !n_sel || !signals || !workspace) {
+    set_error("pfml_standardize_scale: null/empty argument");
+    return -1;
+  }
+  if (panel->lb < 0 || panel->p < 2 || (panel->p & 1)) {
+    set_error("pfml_standardize_scale: need lb >= 0 and even p >= 2 (lb=%d p=%d)", panel->lb, panel->p);
+    return -2;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const PanelView pv = view_of(panel);
+  const int NP = pfml_padded_n(n_max), P = pv.p + 1, nt = pv.lb + 2;
+  StepWs w = carve_step(workspace, workspace_bytes, B, NP, P, nt, pv.K, true, true);
+  if (w.bytes > workspace_bytes) {
+    set_error("pfml_standardize_scale: workspace too small (%zu < %zu bytes; size it with pfml_date_steps_workspace_bytes)",
+              workspace_bytes, w.bytes);
+    return -3;
+  }
+  ProfScope ps(T_STD, s);
+  PFML_TRY(prep_vectors(pv, B, NP, date_t, sel, n_sel, w.v, s));
+  return standardize(pv, B, NP, P, w.ldP, date_t, sel, n_sel, w.v, w.St, nullptr, false, nt, s, signals);
+}
+
+int pfml_omega_batched(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                       double* omega, double* omega_chg, double* m, int* status, void* workspace, size_t workspace_bytes,
+                       void* stream) {
+  if (!omega || !omega_chg) {
+    set_error("pfml_omega_batched: null output");
+    return -1;
+  }
+  StepOpts o;
+  o.omega_out = omega; o.omega_chg_out = omega_chg; o.m_out = m; o.stop_after_omega = true;
+  return date_steps_impl(panel, B, n_max, date_t, sel, n_sel, nullptr, nullptr, nullptr, nullptr, nullptr, status, workspace,
+                         workspace_bytes, (cudaStream_t)stream, o);
+}
+
+int pfml_rtilde_denom_batched(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
+                              const double* omega, const double* omega_chg, double* r_tilde, double* denom, double* risk,
+                              double* tc, int* status, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!omega || !omega_chg) {
+    set_error("pfml_rtilde_denom_batched: null input");
+    return -1;
+  }
+  StepOpts o;
+  o.omega_in = omega; o.omega_chg_in = omega_chg;
+  return date_steps_impl(panel, B, n_max, date_t, sel, n_sel, r_tilde, denom, risk, tc, nullptr, status, workspace,
+                         workspace_bytes, (cudaStream_t)stream, o);
+}
+
 // ---- m_func ----------------------------------------------------------------------------------------
 static MtBufs carve_mt(Carver& c, int B, int NP, double** isl, double** sl) {
   MtBufs m{};
@@ -785,7 +893,7 @@ static EmuWs carve_emu(void* ws, size_t cap, int M, int N, int K, int batch) {
   w.As = c.take<int8_t>(emu_a_slices_bytes(batch, M, K));
   w.Bs = c.take<int8_t>(emu_b_slices_bytes(batch, K, N));
   w.sa = c.take<double>((size_t)batch * M); w.sb = c.take<double>((size_t)batch * N);
-  w.ex = c.take<int>((size_t)batch * N); w.err = c.take<int>(64);
+  w.ex = c.take<int>((size_t)batch * N); w.err = c.take<int>(EMU_ERR_SLOT0 + (size_t)batch);
   w.bytes = c.off;
   return w;
 }
@@ -812,20 +920,20 @@ int pfml_dgemm_emulated(int M, int N, int K, double alpha, const double* A, long
     set_error("pfml_dgemm_emulated: workspace too small (%zu < %zu bytes)", workspace_bytes, w.bytes);
     return -3;
   }
-  PFML_CUDA_OK(cudaMemsetAsync(w.err, 0, sizeof(int), s));
+  PFML_CUDA_OK(cudaMemsetAsync(w.err, 0, sizeof(int) * (EMU_ERR_SLOT0 + (size_t)batch), s));
   PFML_TRY(emu_slice_a(A, lda, sA, M, K, batch, w.As, w.sa, w.err, s));
   PFML_TRY(emu_slice_b(B, ldb, sB, K, N, batch, w.Bs, w.sb, w.ex, w.err, s));
   PFML_TRY(emu_mma(w.As, w.sa, w.Bs, w.sb, M, N, K, batch, alpha, nullptr, 0, beta, beta != 0.0 ? D : nullptr, ldd, sD, D, ldd, sD,
                    w.err, s));
   if (status) {
     PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int), s));
-    fold_emu_error_kernel<<<1, 32, 0, s>>>(1, w.err, status);
+    fold_emu_error_kernel<<<ceil_div(batch, 128), 128, 0, s>>>(batch, w.err, status, 1);
     PFML_CHECK_LAUNCH();
   }
   return 0;
 }
 
-void pfml_set_emulation(int on) { g_use_emu = (on < 0 || on > 2) ? 1 : on; }
+void pfml_set_emulation(int on) { g_use_emu.store((on < 0 || on > 2) ? 1 : on, std::memory_order_relaxed); }
 
 namespace {
 __global__ void pad_identity_kernel(int n, int NP, const double* __restrict__ A, double* __restrict__ Wk) {
@@ -910,10 +1018,10 @@ int pfml_vol_scale(const double* fct_load, const double* fct_cov, const double* 
 }
 
 // ---- profiling ---------------------------------------------------------------------------------------
-void pfml_prof_enable(int on) { g_prof_on = on != 0; }
+void pfml_prof_enable(int on) { g_prof_on.store(on != 0); }
 int pfml_prof_ntags(void) { return N_TAGS; }
 const char* pfml_prof_tag_name(int tag) { return (tag >= 0 && tag < N_TAGS) ? kTagNames[tag] : "?"; }
-long pfml_launch_count(void) { return g_launch_count; }
+long pfml_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
 
 int pfml_prof_collect(double* ms, double* flops, double* launches) {
   PFML_CUDA_OK(cudaDeviceSynchronize());

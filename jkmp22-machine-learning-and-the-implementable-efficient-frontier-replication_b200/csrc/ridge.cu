@@ -20,6 +20,19 @@ int spd_inverse(int B, int NP, double* Wk, double* X, double* T1, int* status, c
 using namespace pfml;
 
 namespace {
+__global__ void bucket_accumulate_kernel(int B, long elems, const double* __restrict__ in, const int* __restrict__ bucket,
+                                         int n_buckets, double* __restrict__ out);
+}
+
+namespace pfml {
+int bucket_accumulate(int B, long elems, const double* in, const int* bucket, int n_buckets, double* out, cudaStream_t s) {
+  bucket_accumulate_kernel<<<dim3(ceil_div(elems, 256), n_buckets), 256, 0, s>>>(B, elems, in, bucket, n_buckets, out);
+  PFML_CHECK_LAUNCH();
+  return 0;
+}
+}  // namespace pfml
+
+namespace {
 
 __device__ __forceinline__ int feat_index(int k, int p, int p_max) {
   // pfml_feat_fun(p) inside pfml_feat_fun(p_max): constant, cos 1..p/2, sin 1..p/2
@@ -27,25 +40,22 @@ __device__ __forceinline__ int feat_index(int k, int p, int p_max) {
   return k == 0 ? 0 : (k <= h ? k : (p_max >> 1) + (k - h));
 }
 
-// out[bucket[b]] += in[b] over dates in order, one thread per element (deterministic left-to-right sums)
+// out[k] += (x_b0 + x_b1 + ...) over the dates b0 < b1 < ... of window k, one thread per (element, window): the reference's
+// left-to-right reduce() (PFML_Search_Coef.py:37-46), formed from the first term, then added to the running sum
 __global__ void bucket_accumulate_kernel(int B, long elems, const double* __restrict__ in, const int* __restrict__ bucket,
                                          int n_buckets, double* __restrict__ out) {
   const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int k = blockIdx.y;
   if (e >= elems) return;
-  int cur = -1;
+  bool any = false;
   double acc = 0.0;
   for (int b = 0; b < B; b++) {
-    const int k = bucket[b];
-    if (k < 0 || k >= n_buckets) continue;
-    if (k != cur) {
-      if (cur >= 0) out[(long)cur * elems + e] += acc;
-      cur = k;
-      acc = in[(long)b * elems + e];      // first term of the reduce(): x0, then x0 + x1, ...
-    } else {
-      acc += in[(long)b * elems + e];
-    }
+    if (bucket[b] != k) continue;
+    const double x = in[(long)b * elems + e];
+    acc = any ? acc + x : x;
+    any = true;
   }
-  if (cur >= 0) out[(long)cur * elems + e] += acc;
+  if (any) out[(long)k * elems + e] += acc;
 }
 
 __global__ void bucket_cumsum_kernel(int n_buckets, long elems, double* __restrict__ x) {
@@ -129,10 +139,8 @@ int pfml_bucket_accumulate(const double* r_tilde, const double* denom, const int
   }
   cudaStream_t s = (cudaStream_t)stream;
   ProfScope ps(T_RIDGE, s);
-  bucket_accumulate_kernel<<<ceil_div(P, 256), 256, 0, s>>>(B, P, r_tilde, bucket, n_buckets, r_sum);
-  PFML_CHECK_LAUNCH();
-  bucket_accumulate_kernel<<<ceil_div((long)P * P, 256), 256, 0, s>>>(B, (long)P * P, denom, bucket, n_buckets, d_sum);
-  PFML_CHECK_LAUNCH();
+  PFML_TRY(bucket_accumulate(B, P, r_tilde, bucket, n_buckets, r_sum, s));
+  PFML_TRY(bucket_accumulate(B, (long)P * P, denom, bucket, n_buckets, d_sum, s));
   return 0;
 }
 

@@ -126,6 +126,18 @@ class DateStepRunner:
                                       self.ws_bytes, _stream_ptr()), "pfml_date_steps")
 
 
+    def run_bucketed(self, bucket, n_buckets, r_sum, d_sum):
+        """The same step with the expanding-window sums fused in (pfml_date_steps_bucketed): ``bucket`` int32 device
+        tensor [b], ``r_sum`` [n_buckets, P] / ``d_sum`` [n_buckets, P, P] are accumulated into."""
+        lib = _lib.load()
+        with torch.cuda.device(self.dp.device):
+            check(lib.pfml_date_steps_bucketed(C.byref(self.dp.struct), self.b, self.n_max, _ptr(self.date_t), _ptr(self.sel),
+                                               _ptr(self.n_sel), _ptr(bucket), int(n_buckets), _ptr(r_sum), _ptr(d_sum),
+                                               _ptr(self.r_tilde), _ptr(self.denom), _ptr(self.risk), _ptr(self.tc),
+                                               _ptr(self.signal_t), _ptr(self.status), _ptr(self.ws), self.ws_bytes, _stream_ptr()),
+                  "pfml_date_steps_bucketed")
+
+
 def date_steps(panel, months, device="cuda:0", dpanel=None):
     """Run the date-steps of ``months`` (month indices into the panel) and return numpy outputs per date."""
     months = list(months)
@@ -143,6 +155,75 @@ def date_steps(panel, months, device="cuda:0", dpanel=None):
                         risk=runner.risk[b].cpu().numpy(), tc=runner.tc[b].cpu().numpy(),
                         signal_t=runner.signal_t[b, :n].cpu().numpy(), ids=panel.ids[sel[b, :n]], status=int(status[b])))
     return out
+
+
+class _StageCall:
+    """Shared set-up of the stage-level entry points: device copies of date_t / sel / n_sel and the date-step workspace."""
+
+    def __init__(self, panel, months, device="cuda:0", dpanel=None):
+        self.lib = _lib.load()
+        self.months = [int(t) for t in months]
+        self.dp = dpanel or DevicePanel(panel, device)
+        self.sel, self.n_sel, self.n_max, self.NP = universe(panel, self.months)
+        dev = self.dp.device
+        self.B, self.P = len(self.months), self.dp.p + 1
+        self.date_t = torch.as_tensor(np.asarray(self.months, dtype=np.int32)).to(dev)
+        self.sel_d = torch.as_tensor(self.sel).to(dev)
+        self.n_sel_d = torch.as_tensor(self.n_sel).to(dev)
+        self.status = torch.zeros(self.B, dtype=torch.int32, device=dev)
+        self.ws_bytes = self.lib.pfml_date_steps_workspace_bytes(C.byref(self.dp.struct), self.B, self.n_max)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
+
+    def head(self):
+        return (C.byref(self.dp.struct), self.B, self.n_max, _ptr(self.date_t), _ptr(self.sel_d), _ptr(self.n_sel_d))
+
+    def tail(self):
+        return (_ptr(self.ws), self.ws_bytes, _stream_ptr())
+
+    def empty(self, *shape):
+        return torch.empty(shape, dtype=torch.float64, device=self.dp.device)
+
+
+def stage_signals(panel, months, device="cuda:0", dpanel=None):
+    """a6 alone (pfml_standardize_scale): signals[tau] = diag(1/vol_scale) s, PFML_Input_Data.py:357-388.
+    Returns one array [lb+2, n, P] per date (columns in feat_all order)."""
+    c = _StageCall(panel, months, device, dpanel)
+    nt = panel.lb + 2
+    out = c.empty(c.B, nt, c.NP, c.P)
+    with torch.cuda.device(c.dp.device):
+        check(c.lib.pfml_standardize_scale(*c.head(), _ptr(out), *c.tail()), "pfml_standardize_scale")
+        torch.cuda.synchronize(c.dp.device)
+    return [out[b, :, :int(c.n_sel[b])].cpu().numpy() for b in range(c.B)]
+
+
+def stage_omega(panel, months, device="cuda:0", dpanel=None):
+    """a3..a8 alone (pfml_omega_batched): omega, omega_chg (PFML_Input_Data.py:455-459) and m (General_functions.py:962)."""
+    c = _StageCall(panel, months, device, dpanel)
+    om, omc, m = c.empty(c.B, c.NP, c.P), c.empty(c.B, c.NP, c.P), c.empty(c.B, c.NP, c.NP)
+    with torch.cuda.device(c.dp.device):
+        check(c.lib.pfml_omega_batched(*c.head(), _ptr(om), _ptr(omc), _ptr(m), _ptr(c.status), *c.tail()), "pfml_omega_batched")
+        torch.cuda.synchronize(c.dp.device)
+    st = c.status.cpu().numpy()
+    return [dict(omega=om[b, :n].cpu().numpy(), omega_chg=omc[b, :n].cpu().numpy(), m=m[b, :n, :n].cpu().numpy(), status=int(st[b]))
+            for b, n in enumerate(int(x) for x in c.n_sel)]
+
+
+def stage_rtilde_denom(panel, months, omegas, omega_chgs, device="cuda:0", dpanel=None):
+    """a9 alone (pfml_rtilde_denom_batched) from given omega / omega_chg [n, P] per date (PFML_Input_Data.py:470-481)."""
+    c = _StageCall(panel, months, device, dpanel)
+    om, omc = np.zeros((c.B, c.NP, c.P)), np.zeros((c.B, c.NP, c.P))
+    for b in range(c.B):
+        om[b, :omegas[b].shape[0]] = omegas[b]
+        omc[b, :omega_chgs[b].shape[0]] = omega_chgs[b]
+    om_d, omc_d = _dev(om, c.dp.device), _dev(omc, c.dp.device)
+    rt, dn, rk, tc = c.empty(c.B, c.P), c.empty(c.B, c.P, c.P), c.empty(c.B, c.P, c.P), c.empty(c.B, c.P, c.P)
+    with torch.cuda.device(c.dp.device):
+        check(c.lib.pfml_rtilde_denom_batched(*c.head(), _ptr(om_d), _ptr(omc_d), _ptr(rt), _ptr(dn), _ptr(rk), _ptr(tc),
+                                              _ptr(c.status), *c.tail()), "pfml_rtilde_denom_batched")
+        torch.cuda.synchronize(c.dp.device)
+    st = c.status.cpu().numpy()
+    return [dict(r_tilde=rt[b].cpu().numpy(), denom=dn[b].cpu().numpy(), risk=rk[b].cpu().numpy(), tc=tc[b].cpu().numpy(),
+                 status=int(st[b])) for b in range(c.B)]
 
 
 def m_func_batched(w, mu, rf, sigma_gam, gam, lam, iterations, device="cuda:0"):

@@ -123,3 +123,25 @@ def test_hp_reals_aim_backtest_match_reference(gold, syn):
         assert relerr(w[t]["w_start"], gold["bt_w_start"][k, sel]) < 1e-10
         assert relerr(np.array([st[t][n] for n in ("inv", "shorting", "turnover", "r", "tc")]), gold["bt_stats"][k]) < 1e-10
     assert abs(w[oos[0]]["w_start"].sum() - 1.0) < 1e-14            # value-weighted start
+
+
+def test_date_step_matches_second_reference_run_n150_p64(syn):
+    """Second reference-run fixture (oracle/make_golden_mid.py): N = 150, p = 64, ragged, Barra ids missing; outputs of every
+    hot date plus omega / omega_chg / m of the last date read from the exec'd script's namespace."""
+    z = np.load(os.path.join(GOLD, "pfml_ref_mid.npz"))
+    panel = panel_from_golden(z, syn)
+    T, N, F = panel.feats.shape
+    rff_x = O.rff(panel.feats.reshape(T * N, F), panel.W).reshape(T, N, -1)
+    vs = O.vol_scale_panel(panel)
+    hot = [int(t) for t in z["hot"]]
+    for k, t in enumerate(hot):
+        last = k == len(hot) - 1
+        o = O.date_step(panel, t, rff_x, vs, keep=last)
+        n = int(z["n_d"][k])
+        for name in ("r_tilde", "denom", "risk", "tc"):
+            assert relerr(o[name], z[name][k]) < 1e-10, (name, k)
+        assert relerr(o["signal_t"], z["signal_t"][k, :n]) < 1e-10
+        if last:
+            assert relerr(o["omega"], z["omega_last"]) < 1e-10
+            assert relerr(o["omega_chg"], z["omega_chg_last"]) < 1e-10
+            assert relerr(o["m"], z["m_last"]) < 1e-10
