@@ -72,9 +72,11 @@ def main():
             worst["m"] = relerr(o["m"], m_last)
     print("oracle vs exec'd PFML_Input_Data.py (N=150, p=64), max rel err:", worst)
     assert max(worst.values()) < 1e-9, worst
+    pdict = panel_to_dict(panel)
+    pdict["panel_feats_q"] = np.round(pdict.pop("panel_feats") * 1000.0).astype(np.uint16)      # 3-decimal ranks (quantize=True)
     np.savez_compressed(os.path.join(gold, "pfml_ref_mid.npz"), r_tilde=r_t, denom=den, risk=risk, tc=tc, signal_t=sig, n_d=n_d,
                         hot=np.asarray(hot), omega_last=omega, omega_chg_last=omega_chg, m_last=m_last,
-                        versions=np.array([np.__version__, pd.__version__]), **panel_to_dict(panel))
+                        versions=np.array([np.__version__, pd.__version__]), **pdict)
     print("wrote tests/golden/pfml_ref_mid.npz", os.path.getsize(os.path.join(gold, "pfml_ref_mid.npz")) // 1024, "KiB")
 
 
