@@ -237,7 +237,8 @@ int pfml_inverse_batched_static(int B, int n, const double* A, double* Ainv, int
  * runs a1 + a2 + B date-steps on the device, downloads the outputs.  feats [T*N][F], W [F][p/2], tr_ld0/
  * mu_ld0/lam/ret_ld1/ivol [T*N], fct_load [T*N][K], fct_cov [T][K][K], barra_has [T*N] (uint8, may be NULL),
  * wealth/rf [T]; date_t/sel/n_sel as above but in host memory.  Output pointers are host memory (pinned
- * memory gives asynchronous copies); risk, tc, signal_t may be NULL. */
+ * memory gives asynchronous copies); risk, tc, signal_t may be NULL.  date_t (lb + 1 <= t < T), n_sel (1..n_max),
+ * sel (0..N-1), K, p and lb are validated on the host before anything is uploaded (-2 with a message). */
 typedef struct {
   int T, N, F, p, K;
   const double *feats, *W, *tr_ld0, *mu_ld0, *lam, *ret_ld1, *fct_load, *fct_cov, *ivol, *wealth, *rf;
@@ -248,6 +249,20 @@ typedef struct {
 int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_max, const int* date_t, const int* sel,
                          const int* n_sel, double* r_tilde, double* denom, double* risk, double* tc,
                          double* signal_t, int* status, int chunk, int device);
+
+/* The same call with the symmetric outputs in PACKED form: risk, tc and denom are symmetric and denom = risk + tc
+ * exactly (PFML_Input_Data.py:473-481), so the upper triangles of risk and tc (row-major, row r holds columns r..P-1,
+ * P (P + 1) / 2 doubles each) carry everything the reference stores per date in a third of the bytes: risk_ut, tc_ut
+ * [B][P (P + 1) / 2].  This is also what crosses PCIe inside pfml_date_steps_host, which rebuilds the full squares in the
+ * caller's buffers with host threads (PFML_HOST_UNPACK_THREADS, default = cores per local rank, at most 16) while the
+ * GPU works on the later chunks; the rebuilt squares are bit-identical to the device-resident ones.
+ * pfml_unpack_upper / pfml_unpack_reals do that rebuild for one date on the calling thread (pure host code):
+ * full [P][P] from ut; risk, tc and denom = risk + tc [P][P] from the two triangles. */
+int pfml_date_steps_host_packed(const pfml_host_block_t* blk, int B, int n_max, const int* date_t, const int* sel,
+                                const int* n_sel, double* r_tilde, double* risk_ut, double* tc_ut, double* signal_t,
+                                int* status, int chunk, int device);
+int pfml_unpack_upper(const double* ut, int P, double* full);
+int pfml_unpack_reals(const double* risk_ut, const double* tc_ut, int P, double* risk, double* tc, double* denom);
 
 /* Device-time accounting with CUDA events (used by bench.py for the live roofline): enable, run, collect.
  * pfml_prof_collect synchronises the device, fills ms/flops/launches [n_tags] and clears the log.

@@ -105,6 +105,10 @@ SIGNATURES = {
     "pfml_date_steps_host": (C.c_int, [C.POINTER(HostBlockStruct), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_int, C.c_int]),
+    "pfml_date_steps_host_packed": (C.c_int, [C.POINTER(HostBlockStruct), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "pfml_unpack_upper": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "pfml_unpack_reals": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "pfml_prof_enable": (None, [C.c_int]),
     "pfml_prof_ntags": (C.c_int, []),
     "pfml_prof_tag_name": (C.c_char_p, [C.c_int]),

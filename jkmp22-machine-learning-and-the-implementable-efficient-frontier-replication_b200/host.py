@@ -62,7 +62,12 @@ class HostBlock:
         self.out = {"r_tilde": mk(B, P), "denom": mk(B, P, P), "risk": mk(B, P, P), "tc": mk(B, P, P),
                     "signal_t": mk(B, NP, P)}
         self.status = torch.zeros(B, dtype=torch.int32)
-        self.d2h_bytes = sum(v.numel() * 8 for v in self.out.values()) + 4 * B
+        self.mk = mk
+        self.packed = None
+        PT = P * (P + 1) // 2
+        # bytes that cross PCIe per call: r_tilde, signal_t and the two packed triangles (both entry points)
+        self.d2h_bytes = 8 * B * (P + NP * P + 2 * PT) + 4 * B
+        self.d2h_bytes_full_squares = sum(v.numel() * 8 for v in self.out.values()) + 4 * B
 
     def run(self, chunk=0, device=0, full_outputs=True):
         lib = _lib.load()
@@ -74,6 +79,33 @@ class HostBlock:
                                        opt("risk"), opt("tc"), opt("signal_t"), C.c_void_p(self.status.data_ptr()),
                                        int(chunk), int(device)), "pfml_date_steps_host")
         return self
+
+
+    def run_packed(self, chunk=0, device=0):
+        """pfml_date_steps_host_packed: r_tilde, signal_t and the packed upper triangles of risk and tc (self.packed)."""
+        lib = _lib.load()
+        B, P = self.B, self.P
+        if self.packed is None:
+            PT = P * (P + 1) // 2
+            self.packed = {"risk_ut": self.mk(B, PT), "tc_ut": self.mk(B, PT)}
+        o, q = self.out, self.packed
+        check(lib.pfml_date_steps_host_packed(C.byref(self.struct), B, self.n_max, C.c_void_p(self.date_t.ctypes.data),
+                                              C.c_void_p(self.sel.ctypes.data), C.c_void_p(self.n_sel.ctypes.data),
+                                              C.c_void_p(o["r_tilde"].data_ptr()), C.c_void_p(q["risk_ut"].data_ptr()),
+                                              C.c_void_p(q["tc_ut"].data_ptr()), C.c_void_p(o["signal_t"].data_ptr()),
+                                              C.c_void_p(self.status.data_ptr()), int(chunk), int(device)),
+              "pfml_date_steps_host_packed")
+        return self
+
+    def unpack(self, b):
+        """risk, tc, denom [P, P] of date b from the packed triangles (pfml_unpack_reals, host only)."""
+        lib = _lib.load()
+        P = self.P
+        risk, tc, denom = (np.empty((P, P)) for _ in range(3))
+        check(lib.pfml_unpack_reals(C.c_void_p(self.packed["risk_ut"][b].data_ptr()), C.c_void_p(self.packed["tc_ut"][b].data_ptr()), P,
+                                    C.c_void_p(risk.ctypes.data), C.c_void_p(tc.ctypes.data), C.c_void_p(denom.ctypes.data)),
+              "pfml_unpack_reals")
+        return risk, tc, denom
 
 
 def date_steps_host(panel, months, chunk=0, device=0, pin=True):

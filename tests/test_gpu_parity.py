@@ -162,6 +162,52 @@ def test_host_entry_point_matches_device_path(dev, syn):
                 assert relerr(y[name], x[name]) < 1e-13, (name, chunk)
 
 
+def test_host_entry_points_bit_identical_to_resident_path(dev, syn):
+    """Full-square entry (packed transfer + host rebuild, several chunks / unpack threads), packed entry + pfml_unpack_reals
+    and the old full-square download all return exactly the bits the device-resident path holds."""
+    import torch
+    host = pkg("host")
+    panel = syn.make_panel(N=100, T=24, p=64, seed=29, ragged=0.04)
+    months = list(range(13, 24))
+    a = dev.date_steps(panel, months)
+    blk = host.HostBlock(panel, months, pin=True)
+    for chunk in (0, 4):
+        for v in blk.out.values():
+            v.fill_(float("nan"))
+        blk.run(chunk=chunk)
+        assert int(blk.status.abs().sum()) == 0
+        for b, x in enumerate(a):
+            n = x["signal_t"].shape[0]
+            for name in ("r_tilde", "denom", "risk", "tc"):
+                assert np.array_equal(blk.out[name][b].numpy(), x[name]), (name, b, chunk)
+            assert np.array_equal(blk.out["signal_t"][b, :n].numpy(), x["signal_t"])
+    # r_tilde + denom only: one triangle travels and is mirrored
+    blk.out["denom"].fill_(float("nan"))
+    blk.run(chunk=3, full_outputs=False)
+    for b, x in enumerate(a):
+        assert np.array_equal(blk.out["denom"][b].numpy(), x["denom"])
+    blk.run_packed(chunk=5)
+    for b, x in enumerate(a):
+        risk, tc, denom = blk.unpack(b)
+        assert np.array_equal(risk, x["risk"]) and np.array_equal(tc, x["tc"]) and np.array_equal(denom, x["denom"])
+    assert blk.d2h_bytes < 0.5 * blk.d2h_bytes_full_squares
+
+
+def test_host_entry_point_validates_before_upload(dev, syn):
+    host = pkg("host")
+    L = pkg("_lib")
+    panel = syn.make_panel(N=70, T=16, p=8, seed=30)
+    for field, bad in (("date_t", 3), ("n_sel", 0), ("n_sel", 10 ** 6), ("sel", -1), ("sel", 70)):
+        blk = host.HostBlock(panel, [13, 14], pin=False)
+        getattr(blk, field).reshape(-1)[0] = bad
+        with pytest.raises(L.PfmlError, match="code -2"):
+            blk.run()
+    blk = host.HostBlock(panel, [13, 14], pin=False)
+    blk.struct.K = 40
+    with pytest.raises(L.PfmlError, match="code -2"):
+        blk.run()
+
+
 def test_full_size_properties(dev, syn):
     """BASELINE metric size (N=500, p=1024): properties that need no oracle run."""
     panel = syn.make_panel(N=500, T=14, p=1024, seed=27)
