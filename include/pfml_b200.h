@@ -144,6 +144,36 @@ int pfml_ridge_grid(const double* r_cum, const double* d_cum, const double* n_cu
                     int n_p, const double* l_vec, int n_l, double* beta, int* status, void* workspace,
                     size_t workspace_bytes, void* stream);
 
+/* e -- the exchange steps of the path over NCCL (one process per GPU; the reference is single-process and has no
+ * counterpart: its year loop PFML_Search_Coef.py:102-137 runs all of this serially).
+ *   communicator   rank 0 calls pfml_comm_unique_id (128 bytes) and hands the id to the other ranks by any host-side
+ *                  means (torch.distributed broadcast, a file, MPI); every rank then calls pfml_comm_init with its
+ *                  device.  The handle is opaque; NCCL is opened at run time from the copy already in the process.
+ *   pfml_comm_allreduce_sums   in-place FP64 sum all-reduce of the per-window partial sums every rank accumulated over
+ *                  ITS dates (pfml_date_steps_bucketed / pfml_bucket_accumulate): r_sum [n_buckets][P],
+ *                  d_sum [n_buckets][P][P], counts [n_buckets] (dates per window, may be NULL)
+ *                  (PFML_Search_Coef.py:77-88, :112-121).  comm NULL or a single rank: no-op.
+ *   pfml_ridge_grid_sharded    pfml_ridge_grid with the (year, lambda) problems of every p dealt over the ranks in
+ *                  contiguous balanced ranges (pfml_ridge_shard_range) and beta / status all-gathered, so every rank
+ *                  returns the full grid (PFML_Search_Coef.py:125-135).  Same arguments and workspace as pfml_ridge_grid.
+ *   pfml_ridge_grid_range      one rank's share without a communicator: the flat (year, lambda) problems
+ *                  [prob_lo, prob_hi) of every p; the other entries of beta / status are left untouched (what
+ *                  pfml_ridge_grid_sharded runs before its all-gather) */
+int pfml_comm_unique_id(void* id128);
+int pfml_comm_init(const void* id128, int rank, int world, int device, void** comm);
+int pfml_comm_rank(void* comm);
+int pfml_comm_world(void* comm);
+int pfml_comm_nccl_version(void);
+int pfml_comm_destroy(void* comm);
+int pfml_comm_allreduce_sums(void* comm, double* r_sum, double* d_sum, double* counts, int P, int n_buckets, void* stream);
+void pfml_ridge_shard_range(int nprob, int rank, int world, int* lo, int* hi);
+int pfml_ridge_grid_range(const double* r_cum, const double* d_cum, const double* n_cum, int Y, int p_max, const int* p_vec_host,
+                          int n_p, const double* l_vec, int n_l, int prob_lo, int prob_hi, double* beta, int* status,
+                          void* workspace, size_t workspace_bytes, void* stream);
+int pfml_ridge_grid_sharded(void* comm, const double* r_cum, const double* d_cum, const double* n_cum, int Y, int p_max,
+                            const int* p_vec_host, int n_p, const double* l_vec, int n_l, double* beta, int* status,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* a15 -- daily cross-sectional OLS of "Estimate Covariance Matrix.py":214-241.  Rows are sorted by day; day d owns
  * rows [day_ptr[d], day_ptr[d+1]) of X [rows][K] and y [rows] (day_ptr: device int64 [n_days+1]).  Outputs
  * coef [n_days][K] (= fct_ret) and the residuals [rows].  A factor whose column is empty that day (exactly
@@ -253,9 +283,10 @@ int pfml_date_steps_host(const pfml_host_block_t* blk, int B, int n_max, const i
 /* The same call with the symmetric outputs in PACKED form: risk, tc and denom are symmetric and denom = risk + tc
  * exactly (PFML_Input_Data.py:473-481), so the upper triangles of risk and tc (row-major, row r holds columns r..P-1,
  * P (P + 1) / 2 doubles each) carry everything the reference stores per date in a third of the bytes: risk_ut, tc_ut
- * [B][P (P + 1) / 2].  This is also what crosses PCIe inside pfml_date_steps_host, which rebuilds the full squares in the
- * caller's buffers with host threads (PFML_HOST_UNPACK_THREADS, default = cores per local rank, at most 16) while the
- * GPU works on the later chunks; the rebuilt squares are bit-identical to the device-resident ones.
+ * [B][P (P + 1) / 2].  With the environment variable PFML_HOST_REBUILD=1 this is also what crosses PCIe inside
+ * pfml_date_steps_host, which then rebuilds the full squares in the caller's buffers with host threads
+ * (PFML_HOST_UNPACK_THREADS, default = cores per local rank, at most 16) while the GPU works on the later chunks; the
+ * rebuilt squares are bit-identical to the device-resident ones (opt-in: the rebuild is host-memory bound).
  * pfml_unpack_upper / pfml_unpack_reals do that rebuild for one date on the calling thread (pure host code):
  * full [P][P] from ut; risk, tc and denom = risk + tc [P][P] from the two triangles. */
 int pfml_date_steps_host_packed(const pfml_host_block_t* blk, int B, int n_max, const int* date_t, const int* sel,

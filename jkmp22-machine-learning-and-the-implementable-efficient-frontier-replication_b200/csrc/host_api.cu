@@ -9,9 +9,10 @@
 // information.  A pack kernel gathers those two triangles (2 x P (P + 1) / 2 doubles instead of 3 P^2: 8.4 MB instead of
 // 25.2 MB per date at P = 1025) and
 //   * pfml_date_steps_host_packed hands them to the caller as they are (the layout of the on-disk tensor store), while
-//   * pfml_date_steps_host rebuilds the three full squares in the caller's buffers with a few host threads, chunk by
-//     chunk, while the GPU is still computing the later chunks (bit-identical to the squares the device holds: the
-//     mirror is a copy and denom is the same IEEE addition the device performs).
+//   * pfml_date_steps_host downloads the full squares by default; with PFML_HOST_REBUILD=1 it receives the triangles and
+//     rebuilds the three squares in the caller's buffers with a few host threads, chunk by chunk, while the GPU is still
+//     computing the later chunks (bit-identical to the squares the device holds: the mirror is a copy and denom is the
+//     same IEEE addition the device performs).  Measured slower than the plain download on the 16-vCPU box, hence opt-in.
 // Device memory comes from a grow-only arena per GPU that is reused across calls; the packed triangles of the full-
 // square entry point land in a grow-only pinned host staging buffer, also per GPU.  Calls for the same GPU serialise
 // on that GPU's arena; calls for different GPUs run concurrently.
@@ -303,8 +304,13 @@ int host_impl(const char* fn, const pfml_host_block_t* blk, int B, int n_max, co
   want.risk = packed_out || o.risk != nullptr;
   want.tc = packed_out || o.tc != nullptr;
   want.sig = o.signal_t != nullptr;
-  static const bool full_download = getenv("PFML_HOST_FULL_DOWNLOAD") && atoi(getenv("PFML_HOST_FULL_DOWNLOAD")) != 0;   // tuning aid
-  want.n_ut = packed_out ? 2 : (full_download ? 0 : ((want.risk && want.tc) ? 2 : 1 + (want.risk ? 1 : 0) + (want.tc ? 1 : 0)));
+  // Full-square entry point: by default the squares themselves are downloaded.  PFML_HOST_REBUILD=1 sends the packed
+  // triangles instead and rebuilds the squares with host threads -- a third of the PCIe bytes, but the transposing
+  // rebuild is host-memory / TLB bound: on the 16-vCPU B200 box it measured 130 ms per 148 dates against 115 ms for the
+  // plain download, so it is opt-in for hosts with more memory bandwidth per GPU.
+  const char* rb = getenv("PFML_HOST_REBUILD");
+  const bool rebuild_squares = rb && atoi(rb) != 0;
+  want.n_ut = packed_out ? 2 : (!rebuild_squares ? 0 : ((want.risk && want.tc) ? 2 : 1 + (want.risk ? 1 : 0) + (want.tc ? 1 : 0)));
 
   // Chunks: uniform, default ceil(B / 6).  Consecutive chunks alternate between compute streams (each with its own
   // workspace): the latency-bound kernels of one chunk (block inverses, small GEMMs of the recursion) overlap the

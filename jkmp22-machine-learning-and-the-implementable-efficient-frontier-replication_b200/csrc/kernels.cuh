@@ -72,6 +72,9 @@ int sym_finish(int B, int P, double* risk, double* tc, double* denom, const int*
 int poison_bad_dates(int B, int P, const int* bad, double* r_tilde, double* denom, double* risk, double* tc, cudaStream_t s);
 int tilde_rows(int B, int NP, int P, const double* in, const int* nsel, const double* sl, double* out, long ldo, long stride_o,
                cudaStream_t s);
+int ridge_grid_range(const double* r_cum, const double* d_cum, const double* n_cum, int Y, int p_max, const int* p_vec_host, int n_p,
+                     const double* l_vec, int n_l, double* beta, int* status, void* workspace, size_t workspace_bytes, cudaStream_t s,
+                     int prob_lo, int prob_hi);
 // out[bucket[b]] += in-order sum of in[b] (ridge.cu; PFML_Search_Coef.py:77-88, :112-121)
 int bucket_accumulate(int B, long elems, const double* in, const int* bucket, int n_buckets, double* out, cudaStream_t s);
 int chain_sum(int B, int NP, int nk, const double* const* bk, const double* b11, const double* g0, long sg, double* wk, double* cbs,

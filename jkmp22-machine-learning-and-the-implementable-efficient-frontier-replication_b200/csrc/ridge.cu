@@ -69,11 +69,12 @@ __global__ void bucket_cumsum_kernel(int n_buckets, long elems, double* __restri
 }
 
 // System matrices of one p for all (year, lambda): Wk[y * n_l + l] = D_cum[y][idx, idx] / n_y + lambda_l I, padded
+// (problem = flat (year, lambda) index prob0 + blockIdx: a rank of a sharded grid works on a contiguous range of them)
 __global__ void ridge_build_kernel(int P, int p, int p_max, int NPp, int n_l, const double* __restrict__ d_cum,
-                                   const double* __restrict__ n_cum, const double* __restrict__ l_vec, double* __restrict__ Wk) {
+                                   const double* __restrict__ n_cum, const double* __restrict__ l_vec, double* __restrict__ Wk, int prob0) {
   const int prob = blockIdx.z, r = blockIdx.y, c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= NPp) return;
-  const int y = prob / n_l, l = prob % n_l;
+  const int y = (prob0 + prob) / n_l, l = (prob0 + prob) % n_l;
   const int q = p + 1;
   double v;
   if (r < q && c < q) {
@@ -89,13 +90,13 @@ __global__ void ridge_build_kernel(int P, int p, int p_max, int NPp, int n_l, co
 __global__ void __launch_bounds__(256)
 ridge_apply_kernel(int P, int p, int p_max, int NPp, int n_l, const double* __restrict__ d_cum, const double* __restrict__ r_cum,
                    const double* __restrict__ n_cum, const double* __restrict__ l_vec, const double* __restrict__ X,
-                   double* __restrict__ beta, int refine) {
+                   double* __restrict__ beta, int refine, int prob0) {
   extern __shared__ double sh[];          // rhs / residual [q], beta [q]
-  const int prob = blockIdx.x, y = prob / n_l, l = prob % n_l, q = p + 1;
+  const int prob = blockIdx.x, y = (prob0 + prob) / n_l, l = (prob0 + prob) % n_l, q = p + 1;
   double* res = sh;
   double* bt = sh + q;
   const double inv_n = 1.0 / n_cum[y];
-  double* out = beta + (long)prob * q;
+  double* out = beta + (long)(prob0 + prob) * q;
   for (int i = threadIdx.x; i < q; i += blockDim.x) {
     res[i] = r_cum[(long)y * P + feat_index(i, p, p_max)] / n_cum[y];
     bt[i] = refine ? out[i] : 0.0;
@@ -128,6 +129,60 @@ ridge_apply_kernel(int P, int p, int p_max, int NPp, int n_l, const double* __re
 }
 
 }  // namespace
+
+namespace pfml {
+// the grid restricted to the flat (year, lambda) problems [prob_lo, prob_hi) of every p; beta / status are indexed as in
+// the full grid, entries of other problems are left untouched
+int ridge_grid_range(const double* r_cum, const double* d_cum, const double* n_cum, int Y, int p_max, const int* p_vec_host, int n_p,
+                     const double* l_vec, int n_l, double* beta, int* status, void* workspace, size_t workspace_bytes, cudaStream_t s,
+                     int prob_lo, int prob_hi) {
+  if (!r_cum || !d_cum || !n_cum || !p_vec_host || !l_vec || !beta || !workspace || Y <= 0 || n_p <= 0 || n_l <= 0) {
+    set_error("pfml_ridge_grid: null/empty argument");
+    return -1;
+  }
+  if (workspace_bytes < pfml_ridge_grid_workspace_bytes(Y, p_max, n_l)) {
+    set_error("pfml_ridge_grid: workspace too small");
+    return -3;
+  }
+  const int nprob = Y * n_l;
+  if (prob_lo < 0 || prob_hi > nprob || prob_lo > prob_hi) {
+    set_error("pfml_ridge_grid: problem range [%d, %d) outside [0, %d)", prob_lo, prob_hi, nprob);
+    return -2;
+  }
+  for (int ip = 0; ip < n_p; ip++) {
+    const int p = p_vec_host[ip];
+    if (p < 2 || (p & 1) || p > p_max) {
+      set_error("pfml_ridge_grid: p = %d must be even and in [2, p_max = %d]", p, p_max);
+      return -2;
+    }
+  }
+  ProfScope ps(T_RIDGE, s);
+  const int P = p_max + 1, mine = prob_hi - prob_lo;
+  const size_t per = ((size_t)nprob * pfml_padded_n(P) * pfml_padded_n(P) * sizeof(double) + 255) / 256 * 256;
+  double* Wk = (double*)workspace;
+  double* X = (double*)((char*)workspace + per);
+  double* T1 = (double*)((char*)workspace + 2 * per);
+  long off = 0;
+  for (int ip = 0; ip < n_p; ip++) {
+    const int p = p_vec_host[ip], q = p + 1;
+    if (mine > 0) {
+      int* st = status ? status + (long)ip * nprob + prob_lo : nullptr;
+      if (st) PFML_CUDA_OK(cudaMemsetAsync(st, 0, sizeof(int) * mine, s));
+      const int NPp = pfml_padded_n(q);
+      ridge_build_kernel<<<dim3(ceil_div(NPp, 128), NPp, mine), 128, 0, s>>>(P, p, p_max, NPp, n_l, d_cum, n_cum, l_vec, Wk, prob_lo);
+      PFML_CHECK_LAUNCH();
+      PFML_TRY(spd_inverse(mine, NPp, Wk, X, T1, st, s));
+      for (int pass = 0; pass < 2; pass++) {
+        ridge_apply_kernel<<<mine, 256, 2 * q * sizeof(double), s>>>(P, p, p_max, NPp, n_l, d_cum, r_cum, n_cum, l_vec, X, beta + off,
+                                                                     pass, prob_lo);
+        PFML_CHECK_LAUNCH();
+      }
+    }
+    off += (long)nprob * q;
+  }
+  return 0;
+}
+}  // namespace pfml
 
 extern "C" {
 
@@ -163,44 +218,26 @@ size_t pfml_ridge_grid_workspace_bytes(int Y, int p_max, int n_l) {
   return 3 * (((size_t)Y * n_l * NPp * NPp * sizeof(double) + 255) / 256 * 256);
 }
 
+// rank r of `world` solves the flat (year, lambda) problems [lo, hi) of every p: contiguous in beta, balanced to +-1 problem
+void pfml_ridge_shard_range(int nprob, int rank, int world, int* lo, int* hi) {
+  if (world < 1) world = 1;
+  if (rank < 0) rank = 0;
+  *lo = (int)((long)nprob * rank / world);
+  *hi = (int)((long)nprob * (rank + 1) / world);
+}
+
+int pfml_ridge_grid_range(const double* r_cum, const double* d_cum, const double* n_cum, int Y, int p_max, const int* p_vec_host,
+                          int n_p, const double* l_vec, int n_l, int prob_lo, int prob_hi, double* beta, int* status, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+  return ridge_grid_range(r_cum, d_cum, n_cum, Y, p_max, p_vec_host, n_p, l_vec, n_l, beta, status, workspace, workspace_bytes,
+                          (cudaStream_t)stream, prob_lo, prob_hi);
+}
+
 int pfml_ridge_grid(const double* r_cum, const double* d_cum, const double* n_cum, int Y, int p_max, const int* p_vec_host,
                     int n_p, const double* l_vec, int n_l, double* beta, int* status, void* workspace, size_t workspace_bytes,
                     void* stream) {
-  if (!r_cum || !d_cum || !n_cum || !p_vec_host || !l_vec || !beta || !workspace || Y <= 0 || n_p <= 0 || n_l <= 0) {
-    set_error("pfml_ridge_grid: null/empty argument");
-    return -1;
-  }
-  if (workspace_bytes < pfml_ridge_grid_workspace_bytes(Y, p_max, n_l)) {
-    set_error("pfml_ridge_grid: workspace too small");
-    return -3;
-  }
-  cudaStream_t s = (cudaStream_t)stream;
-  ProfScope ps(T_RIDGE, s);
-  const int P = p_max + 1, nprob = Y * n_l;
-  const size_t per = ((size_t)nprob * pfml_padded_n(P) * pfml_padded_n(P) * sizeof(double) + 255) / 256 * 256;
-  double* Wk = (double*)workspace;
-  double* X = (double*)((char*)workspace + per);
-  double* T1 = (double*)((char*)workspace + 2 * per);
-  if (status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * nprob * n_p, s));
-  long off = 0;
-  for (int ip = 0; ip < n_p; ip++) {
-    const int p = p_vec_host[ip], q = p + 1;
-    if (p < 2 || (p & 1) || p > p_max) {
-      set_error("pfml_ridge_grid: p = %d must be even and in [2, p_max = %d]", p, p_max);
-      return -2;
-    }
-    const int NPp = pfml_padded_n(q);
-    ridge_build_kernel<<<dim3(ceil_div(NPp, 128), NPp, nprob), 128, 0, s>>>(P, p, p_max, NPp, n_l, d_cum, n_cum, l_vec, Wk);
-    PFML_CHECK_LAUNCH();
-    PFML_TRY(spd_inverse(nprob, NPp, Wk, X, T1, status ? status + (long)ip * nprob : nullptr, s));
-    for (int pass = 0; pass < 2; pass++) {
-      ridge_apply_kernel<<<nprob, 256, 2 * q * sizeof(double), s>>>(P, p, p_max, NPp, n_l, d_cum, r_cum, n_cum, l_vec, X,
-                                                                    beta + off, pass);
-      PFML_CHECK_LAUNCH();
-    }
-    off += (long)nprob * q;
-  }
-  return 0;
+  return ridge_grid_range(r_cum, d_cum, n_cum, Y, p_max, p_vec_host, n_p, l_vec, n_l, beta, status, workspace, workspace_bytes,
+                          (cudaStream_t)stream, 0, Y * n_l);
 }
 
 }  // extern "C"

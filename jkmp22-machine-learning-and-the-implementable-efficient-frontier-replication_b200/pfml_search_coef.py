@@ -66,8 +66,11 @@ def bucket_sums(r_tilde, denom, bucket, n_buckets, r_sum=None, d_sum=None):
     return r_sum, d_sum
 
 
-def ridge_grid(r_cum, d_cum, n_cum, p_vec, l_vec):
-    """beta for every (year, p, lambda) from running sums r_cum [Y,P], d_cum [Y,P,P], n_cum [Y] (device tensors)."""
+def ridge_grid(r_cum, d_cum, n_cum, p_vec, l_vec, comm=None, prob_range=None):
+    """beta for every (year, p, lambda) from running sums r_cum [Y,P], d_cum [Y,P,P], n_cum [Y] (device tensors).
+    With a ``comm`` (comm.Communicator) the problems are dealt over its ranks and beta is all-gathered
+    (pfml_ridge_grid_sharded); every rank returns the whole grid.  ``prob_range`` = (lo, hi) solves only that range of
+    the flat (year, lambda) index (pfml_ridge_grid_range; the rest of beta is zero)."""
     lib = _lib.load()
     dev = d_cum.device
     Y, P = r_cum.shape
@@ -76,13 +79,19 @@ def ridge_grid(r_cum, d_cum, n_cum, p_vec, l_vec):
     l_dev = torch.as_tensor(np.asarray(l_vec, dtype=np.float64)).to(dev)
     n_l = len(l_vec)
     total = int(sum(Y * n_l * (int(p) + 1) for p in p_arr))
-    beta = torch.empty(total, dtype=torch.float64, device=dev)
+    beta = torch.zeros(total, dtype=torch.float64, device=dev)
     status = torch.zeros(len(p_arr) * Y * n_l, dtype=torch.int32, device=dev)
     nbytes = lib.pfml_ridge_grid_workspace_bytes(Y, p_max, n_l)
     ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib.pfml_ridge_grid(_ptr(r_cum), _ptr(d_cum), _ptr(n_cum), Y, p_max, C.c_void_p(p_arr.ctypes.data), len(p_arr),
-                                  _ptr(l_dev), n_l, _ptr(beta), _ptr(status), _ptr(ws), nbytes, _stream()), "pfml_ridge_grid")
+        if prob_range is not None:
+            check(lib.pfml_ridge_grid_range(_ptr(r_cum), _ptr(d_cum), _ptr(n_cum), Y, p_max, C.c_void_p(p_arr.ctypes.data), len(p_arr),
+                                            _ptr(l_dev), n_l, int(prob_range[0]), int(prob_range[1]), _ptr(beta), _ptr(status),
+                                            _ptr(ws), nbytes, _stream()), "pfml_ridge_grid_range")
+        else:
+            check(lib.pfml_ridge_grid_sharded(comm.handle if comm is not None else None, _ptr(r_cum), _ptr(d_cum), _ptr(n_cum), Y,
+                                              p_max, C.c_void_p(p_arr.ctypes.data), len(p_arr), _ptr(l_dev), n_l, _ptr(beta),
+                                              _ptr(status), _ptr(ws), nbytes, _stream()), "pfml_ridge_grid_sharded")
     out, off = {}, 0
     for p in p_arr:
         q = int(p) + 1
@@ -91,12 +100,34 @@ def ridge_grid(r_cum, d_cum, n_cum, p_vec, l_vec):
     return out, status.view(len(p_arr), Y, n_l)
 
 
-def search_coef(r_tilde, denom, month_ends, hp_years, p_vec, l_vec, device="cuda:0", group=None):
+def coef_from_sums(r_sum, d_sum, cnt, p_vec, l_vec, comm=None, group=None, reduce=True):
+    """Second half of the year loop (PFML_Search_Coef.py:112-135) from per-window partial sums of THIS RANK's dates:
+    all-reduce over the ranks (``comm``: the library's NCCL communicator; ``group``: a torch.distributed group, used by
+    the CPU/gloo tests), running sums over the windows, ridge grid (sharded over ``comm``).  Tensors are modified in place."""
+    lib = _lib.load()
+    dev = d_sum.device
+    nb, P = r_sum.shape
+    if reduce and comm is not None:
+        comm.allreduce_sums(r_sum, d_sum, cnt)
+    elif reduce and group is not None:
+        import torch.distributed as dist
+        for t in (r_sum, d_sum, cnt):
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group if group is not True else None)
+    if (comm is not None or group is not None) and bool((cnt == 0).any()):
+        raise ValueError("empty window (quirk Q13)")
+    with torch.cuda.device(dev):
+        check(lib.pfml_bucket_cumsum(_ptr(r_sum), _ptr(d_sum), P, nb, _stream()), "pfml_bucket_cumsum")
+    n_cum = torch.cumsum(cnt, 0)
+    return ridge_grid(r_sum[1:], d_sum[1:], n_cum[1:].contiguous(), p_vec, l_vec, comm=comm)
+
+
+def search_coef(r_tilde, denom, month_ends, hp_years, p_vec, l_vec, device="cuda:0", group=None, comm=None):
     """The loop of PFML_Search_Coef.py:60-137 for one g.
 
     r_tilde [T,P], denom [T,P,P]: numpy arrays or device tensors holding THIS RANK's dates (``month_ends`` [T]);
-    with a torch.distributed ``group`` the per-window partial sums of all ranks are combined by an all-reduce
-    (the one exchange step of the path).  Returns ``{year: {p: beta[n_lambda, p+1] (numpy)}}``."""
+    with ``comm`` (comm.Communicator: NCCL through the C ABI) or a torch.distributed ``group`` the per-window partial
+    sums of all ranks are combined by an all-reduce (the one exchange step of the path); with ``comm`` the ridge
+    problems are also dealt over the ranks and beta all-gathered.  Returns ``{year: {p: beta[n_lambda, p+1] (numpy)}}``."""
     lib = _lib.load()
     dev = torch.device(device)
     rt = r_tilde if torch.is_tensor(r_tilde) else torch.as_tensor(np.ascontiguousarray(r_tilde)).to(dev)
@@ -104,8 +135,9 @@ def search_coef(r_tilde, denom, month_ends, hp_years, p_vec, l_vec, device="cuda
     P = rt.shape[1]
     hp_sorted = sorted(int(y) for y in hp_years)
     nb = len(hp_sorted) + 1
+    multi = group is not None or comm is not None
     if len(month_ends):
-        bucket, _ = window_buckets(month_ends, hp_years) if group is None else (_rank_buckets(month_ends, hp_sorted), None)
+        bucket, _ = window_buckets(month_ends, hp_years) if not multi else (_rank_buckets(month_ends, hp_sorted), None)
     else:
         bucket = np.zeros(0, dtype=np.int32)
     counts = np.bincount(bucket[bucket >= 0], minlength=nb).astype(np.float64)
@@ -114,21 +146,17 @@ def search_coef(r_tilde, denom, month_ends, hp_years, p_vec, l_vec, device="cuda
     if len(bucket):
         bucket_sums(rt, dn, bucket, nb, r_sum, d_sum)
     cnt = torch.as_tensor(counts).to(dev)
-    if group is not None:
-        import torch.distributed as dist
-        for t in (r_sum, d_sum, cnt):
-            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group if group is not True else None)
-        if bool((cnt == 0).any()):
-            raise ValueError("empty window (quirk Q13)")
-    with torch.cuda.device(dev):
-        check(lib.pfml_bucket_cumsum(_ptr(r_sum), _ptr(d_sum), P, nb, _stream()), "pfml_bucket_cumsum")
-    n_cum = torch.cumsum(cnt, 0)
-    betas, status = ridge_grid(r_sum[1:].contiguous(), d_sum[1:].contiguous(), n_cum[1:].contiguous(), p_vec, l_vec)
+    betas, status = coef_from_sums(r_sum, d_sum, cnt, p_vec, l_vec, comm=comm, group=group)
     torch.cuda.synchronize(dev)
     coef = {}
     for k, year in enumerate(hp_sorted):
         coef[year] = {int(p): betas[int(p)][k].cpu().numpy() for p in p_vec}
     return coef
+
+
+def rank_buckets(month_ends, hp_sorted):
+    """Windows of a rank's own dates (no emptiness check: that is global, after the all-reduce)."""
+    return _rank_buckets(month_ends, hp_sorted)
 
 
 def _rank_buckets(month_ends, hp_sorted):

@@ -171,7 +171,8 @@ def test_host_entry_points_bit_identical_to_resident_path(dev, syn):
     months = list(range(13, 24))
     a = dev.date_steps(panel, months)
     blk = host.HostBlock(panel, months, pin=True)
-    for chunk in (0, 4):
+    for chunk, rebuild in ((0, "1"), (4, "1"), (4, "0")):
+        os.environ["PFML_HOST_REBUILD"] = rebuild          # packed transfer + host rebuild / plain download of the squares
         for v in blk.out.values():
             v.fill_(float("nan"))
         blk.run(chunk=chunk)
@@ -182,8 +183,10 @@ def test_host_entry_points_bit_identical_to_resident_path(dev, syn):
                 assert np.array_equal(blk.out[name][b].numpy(), x[name]), (name, b, chunk)
             assert np.array_equal(blk.out["signal_t"][b, :n].numpy(), x["signal_t"])
     # r_tilde + denom only: one triangle travels and is mirrored
+    os.environ["PFML_HOST_REBUILD"] = "1"
     blk.out["denom"].fill_(float("nan"))
     blk.run(chunk=3, full_outputs=False)
+    os.environ.pop("PFML_HOST_REBUILD")
     for b, x in enumerate(a):
         assert np.array_equal(blk.out["denom"][b].numpy(), x["denom"])
     blk.run_packed(chunk=5)
