@@ -3,15 +3,20 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--dates B]
 
-A "step" is one batch of B date-steps (one iteration each of the loop PFML_Input_Data.py:318-491: Sigma,
-Lambda, m_func, standardise, chains, solves, r_tilde / risk / tc / denom) on one GPU.  Dates are independent,
-so ranks shard them with no data-path collective (weak scaling: every rank runs its own B dates per step).
+A "step" is one batch of B date-steps per GPU (one iteration each of the loop PFML_Input_Data.py:318-491: Sigma,
+Lambda, m_func, standardise, chains, solves, r_tilde / risk / tc / denom) WITH the expanding-window sums of
+PFML_Search_Coef.py:77-121 fused into the a9 finish kernel and, at N > 1, the FP64 NCCL all-reduce of those sums
+(pfml_comm_allreduce_sums, the one exchange step of the path) inside the timed region.  Dates are independent, so every
+rank runs its own B dates per step (weak scaling).
 
 Printed JSON line (rank 0): value = whole-job date-steps/s with inputs resident in HBM; e2e = the same through
-pfml_date_steps_host (pinned HOST buffers in, HOST buffers out, H2D/D2H inside the timed region); roofline = the
-dominant kernel (the FP64-equivalent batched GEMM on the INT8 tensor cores) against the tensor-pipe ceiling derived
-from MEASURED_PEAKS.json, with the cuBLAS DGEMM peak measured in this run beside it; cpu_baseline = the
-numpy oracle (a port of the reference's algorithm) on the host cores.  --impl reference times only that CPU arm.
+pfml_date_steps_host_packed (pinned HOST buffers in and out, H2D/D2H inside the timed region; the symmetric outputs
+travel as packed upper triangles, lossless); roofline = the dominant kernel (the FP64-equivalent batched GEMM on the
+INT8 tensor cores) with SURVEY 8(d)'s algorithmic flops against the INT8 tensor-pipe ceiling MEASURED in this run
+(pfml_int8_mma_probe), the cuBLAS DGEMM peak measured beside it; hp_grid = the whole C3 + C4 pipeline (360 months x 3 g
+date-steps -> window sums -> all-reduce -> ridge grid dealt over ranks -> beta all-gather) wall-time at N GPUs next to the
+CPU arm; hbm_rows = the HBM-bound kernels (C2 covariance estimator, RFF) in GB/s; cpu_baseline = the numpy oracle (a
+port of the reference's algorithm) on the host cores.  --impl reference times only that CPU arm.
 """
 from __future__ import annotations
 
@@ -35,6 +40,7 @@ PKG = "jkmp22-machine-learning-and-the-implementable-efficient-frontier-replicat
 N_STOCKS, P_FEAT = 500, 1024
 METRIC = "PFML date-steps/sec (r_tilde+denom, N=500, p=1024)"
 UNIT = "date-steps/s"
+WORKLOAD = "PFML date-step N=500 p=1024 (P=1025), lb=11, 10 m_func iterations (BASELINE configs[2] at the metric's p)"
 
 
 def official_flops_per_date(n=N_STOCKS, P=P_FEAT + 1):
@@ -157,7 +163,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "PFML date-step N=500 p=1024 (P=1025), lb=11, 10 m_func iterations", "dates_per_step": per_step},
+        "config": {"workload": WORKLOAD}, "details": {"dates_per_step": per_step},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference algorithm restated in numpy/scipy (oracle/pfml_oracle.py), OpenBLAS threads = all host cores; "
@@ -165,34 +171,165 @@ def run_reference(args, rank, world):
                 "faster than the reference script itself"}))
 
 
-def hp_grid_walltime(torch, dev, runner, B):
-    """hp-grid wall-time (BASELINE metric, second half): PFML_Search_Coef.py over the step's own r_tilde / denom,
-    treated as B consecutive months: expanding-window sums + ridge solves for 15 lambda x p in {64..1024} x all
-    complete years, on the device; the same grid for ONE year on the host (numpy LU, all cores) for comparison."""
-    sc = importlib.import_module(PKG + ".pfml_search_coef")
+def algorithmic_flops_emu_per_date(n=N_STOCKS, P=P_FEAT + 1):
+    """SURVEY 8(d) work of the launches that run on the INT8 tensor cores: 11 chain products 2n^3, 14 n x n x P products
+    2n^2 P (12 sums + 2 solves) and the two symmetric a9 contractions n P^2 each (only the upper triangle is formed)."""
+    return 11 * 2 * n ** 3 + 14 * 2 * n * n * P + 2 * n * P * P
+
+
+C3_MONTHS, C3_G = 360, 3
+C4_P_VEC = [64, 128, 256, 512, 1024]
+C4_L_VEC = [0.0] + list(np.exp(np.linspace(-10, 10, 14)))
+
+
+def hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, batch):
+    """hp-grid wall-time (BASELINE metric, second half; configs[2] + configs[3]): N = 500, 360 months, 3 bandwidths g,
+    p_max = 1024, 15 lambda x p in {64..1024} x every complete yearly refit -- host panel in, beta on the host out:
+    date-steps sharded over the ranks with the window sums fused in, NCCL all-reduce of the sums, ridge problems dealt over
+    the ranks, beta all-gathered (strong scaling: the work is fixed, ranks split it)."""
     syn = importlib.import_module(PKG + ".synthetic")
+    pl = importlib.import_module(PKG + ".pfml_pipeline")
+    panel = syn.make_panel(N=N_STOCKS, T=syn.LB + 2 + C3_MONTHS, p=P_FEAT, seed=303, g=float(np.exp(-3.0)), start="1990-01")
+    months = [int(t) for t in panel.hot_months()]
+    me = panel.month_ends[months]
+    y0 = int(str(me[0])[:4])
+    years = list(range(y0 + 2, int(str(me[-1])[:4]) + 1))                # burn-in = the first calendar year (11 months)
+    rng = np.random.default_rng(304)
+    Ws = [np.sqrt(g) * rng.standard_normal(panel.W.shape) for g in np.exp([-3.0, -2.0, -1.0])]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    tm = {}
+    pl.hp_grid_pipeline(panel, Ws[:1], months[:min(len(months), 40)], years[:1], C4_P_VEC, C4_L_VEC, comm=comm, device=dev, batch=batch)  # warm-up
+    barrier()
+    t0 = time.perf_counter()
+    coef = pl.hp_grid_pipeline(panel, Ws, months, years, C4_P_VEC, C4_L_VEC, comm=comm, device=dev, batch=batch, timing=tm)
+    barrier()
+    wall = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(wall, op=dist.ReduceOp.MAX)
+    out = {"workload": f"C3 + C4: N={N_STOCKS}, {len(months)} months x {C3_G} g date-steps (p={P_FEAT}) -> {len(years)} yearly refits x "
+                       f"{len(C4_L_VEC)} lambda x p in {C4_P_VEC}",
+           "n_gpus": world, "scaling": "strong", "wall_s": float(wall.item()), "date_steps": len(months) * C3_G,
+           "ridge_solves": len(years) * len(C4_L_VEC) * len(C4_P_VEC) * C3_G,
+           "phases_rank0_s": {k: round(v, 4) for k, v in tm.items() if k.endswith("_s")},
+           "allreduce_bytes": tm.get("allreduce_bytes", 0),
+           "includes": "H2D of this rank's panel slice, RFF + vol_scale, date-steps with fused window sums, NCCL all-reduce, running "
+                       "sums, gather of the pfml_feat_fun(p) sub-matrices, SPD inverses + refinement, beta all-gather, D2H of beta"}
+    if world > 1 and rank == 0:
+        # sharded vs unsharded on the first bandwidth: FP64 summation order only
+        one = pl.hp_grid_pipeline(panel, Ws[:1], months, years, C4_P_VEC, C4_L_VEC, comm=None, device=dev, batch=batch)
+        worst = 0.0
+        for y in years:
+            for p in C4_P_VEC:
+                for j in range(1, len(C4_L_VEC)):
+                    worst = max(worst, float(np.max(np.abs(coef[0][y][p][j] - one[0][y][p][j])) / np.max(np.abs(one[0][y][p][j]))))
+        out["beta_max_rel_diff_vs_1gpu_lambda_gt_0"] = worst
+    if rank != 0:
+        return out
+    # CPU arm on a bounded sample, extrapolated linearly (date-steps and refits are independent): numpy oracle, all BLAS threads
     import pfml_oracle as O
-    month_ends = syn.month_end_range("1990-01", B)
-    years = list(range(1993, 1990 + B // 12 + 1))
-    p_vec = [64, 128, 256, 512, 1024]
-    l_vec = [0.0] + list(np.exp(np.linspace(-10, 10, 14)))
-    rt, dn = runner.r_tilde, runner.denom
-    sc.search_coef(rt, dn, month_ends, years, p_vec, l_vec, device=dev)          # warm-up
-    torch.cuda.synchronize(dev)
-    t0 = time.perf_counter()
-    coef = sc.search_coef(rt, dn, month_ends, years, p_vec, l_vec, device=dev)
-    torch.cuda.synchronize(dev)
-    gpu_s = time.perf_counter() - t0
     use_all_host_threads()
+    small = make_bench_panel(syn, 3, 305)
+    T, N, F = small.feats.shape
+    rff_x = O.rff(small.feats.reshape(T * N, F), small.W).reshape(T, N, -1)
+    vs = O.vol_scale_panel(small)
     t0 = time.perf_counter()
-    ref = O.search_coef(rt.cpu().numpy(), dn.cpu().numpy(), month_ends, years[:1], p_vec, l_vec)
-    cpu_s_per_year = time.perf_counter() - t0
-    y, p = years[0], 1024
-    err = max(float(np.max(np.abs(coef[y][p][j] - ref[y][p][j])) / np.max(np.abs(ref[y][p][j]))) for j in range(1, len(l_vec)))
-    return {"years": len(years), "n_lambda": len(l_vec), "p_vec": p_vec, "solves": len(years) * len(l_vec) * len(p_vec),
-            "gpu_wall_s": gpu_s, "cpu_port_wall_s_per_year": cpu_s_per_year, "cpu_port_wall_s_extrapolated": cpu_s_per_year * len(years),
-            "speedup_vs_cpu_port": cpu_s_per_year * len(years) / gpu_s, "max_rel_err_vs_cpu_p1024_lambda_gt_0": err,
-            "includes": "bucket sums, cumulative sums, gather of the pfml_feat_fun(p) sub-matrices, inverses, refinement, D2H of beta"}
+    for t in small.hot_months():
+        O.date_step(small, int(t), rff_x, vs)
+    cpu_date_s = (time.perf_counter() - t0) / len(small.hot_months())
+    Pn = P_FEAT + 1
+    Tr = 36
+    r_t = rng.standard_normal((Tr, Pn)) * 1e-3
+    A = rng.standard_normal((Tr, Pn, 4)) * 0.2
+    dn = np.einsum("tik,tjk->tij", A, A)
+    dn[:, np.arange(Pn), np.arange(Pn)] += 1e-2
+    me_s = syn.month_end_range("1990-01", Tr)
+    t0 = time.perf_counter()
+    O.search_coef(r_t, dn, me_s, [1993], C4_P_VEC, C4_L_VEC)
+    cpu_year_s = time.perf_counter() - t0
+    cpu_total = cpu_date_s * len(months) * C3_G + cpu_year_s * len(years) * C3_G
+    out["cpu_port"] = {"cores": os.cpu_count(), "s_per_date_step": cpu_date_s, "s_per_yearly_refit": cpu_year_s,
+                       "wall_s_extrapolated": cpu_total,
+                       "sample": f"{len(small.hot_months())} date-steps and 1 yearly refit (all p, all lambda) timed, extrapolated to "
+                                 f"{len(months) * C3_G} date-steps and {len(years) * C3_G} refits"}
+    out["speedup_vs_cpu_port"] = cpu_total / out["wall_s"]
+    out["north_star_target"] = ">= 50x the reference's host-CPU time at 8 GPUs"
+    return out
+
+
+def hbm_rows(torch, dev, lib):
+    """The HBM-bound rows of the path (north_star item 5): achieved GB/s = algorithmic bytes / CUDA-event time.
+    C2: 500 stocks x 5 040 trading days, K = 25 factors (a15 daily OLS, a16 factor covariance, a17 EWMA vol); a1: RFF of the
+    C3 panel (186 500 rows x 115 characteristics -> 1 024 features)."""
+    import ctypes as C
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm = float(peaks.get("hbm_gbs", 6500.0))
+    ptr = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def timed(fn, reps=5):
+        fn(); fn()
+        best = 1e30
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize(dev)
+            best = min(best, e0.elapsed_time(e1))
+        return best
+
+    out = {"hbm_peak_gbs": hbm, "hbm_peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6500 GB/s"}
+    g = torch.Generator(device=dev).manual_seed(1)
+    D, n, K = 5040, 500, 25
+    rows = D * n
+    X = torch.randn(rows, K, dtype=torch.float64, device=dev, generator=g)
+    X[:, :12] = 0.0
+    X[torch.arange(rows, device=dev), torch.randint(0, 12, (rows,), device=dev, generator=g)] = 1.0      # one-hot industries
+    y = 0.01 * torch.randn(rows, dtype=torch.float64, device=dev, generator=g)
+    day_ptr = torch.arange(0, rows + 1, n, dtype=torch.int64, device=dev)
+    coef = torch.empty(D, K, dtype=torch.float64, device=dev)
+    resid = torch.empty(rows, dtype=torch.float64, device=dev)
+    status = torch.zeros(D, dtype=torch.int32, device=dev)
+    ms = timed(lambda: lib.pfml_xs_ols_daily(ptr(X), ptr(y), ptr(day_ptr), D, K, ptr(coef), ptr(resid), ptr(status), st))
+    by = rows * (K + 2) * 8 + D * K * 8                     # X and y read once, residuals written, coefficients written
+    out["a15_xs_ols_daily"] = {"ms": ms, "algorithmic_bytes": by, "gbs": by / ms * 1e-6, "frac_of_hbm_peak": by / ms * 1e-6 / hbm,
+                               "days": D, "stocks_per_day": n, "K": K}
+    n_calc, obs = 240, 2520
+    ends = torch.linspace(obs - 1, D - 1, n_calc, device=dev).to(torch.int32)
+    wc = torch.as_tensor((0.5 ** (1 / 378)) ** np.arange(obs, 0, -1)).to(dev)
+    wv = torch.as_tensor((0.5 ** (1 / 126)) ** np.arange(obs, 0, -1)).to(dev)
+    cov = torch.empty(n_calc, K, K, dtype=torch.float64, device=dev)
+    ms = timed(lambda: lib.pfml_wcov_wcor(ptr(coef), ptr(ends), n_calc, K, obs, ptr(wc), ptr(wv), 21.0, ptr(cov), st))
+    by = n_calc * (obs * K * 8 + 2 * obs * 8)
+    out["a16_wcov_wcor"] = {"ms": ms, "algorithmic_bytes": by, "gbs": by / ms * 1e-6, "calc_dates": n_calc, "window": obs,
+                            "note": "the D x K factor-return matrix (1 MB) stays in L2: bound by L2 / the K x K accumulation, not HBM"}
+    series_ptr = torch.arange(0, rows + 1, D, dtype=torch.int64, device=dev)
+    vol = torch.empty(rows, dtype=torch.float64, device=dev)
+    lam = 0.5 ** (1 / 126)
+    ms = timed(lambda: lib.pfml_ewma_vol(ptr(resid), ptr(series_ptr), n, C.c_double(lam), 63, ptr(vol), st))
+    by = 2 * rows * 8
+    out["a17_ewma_vol"] = {"ms": ms, "algorithmic_bytes": by, "gbs": by / ms * 1e-6, "series": n, "length": D,
+                           "note": "20 MB in, 20 MB out; each series is a 5 040-step dependent recurrence (un-fused multiply and add "
+                                   "like the reference's numba kernel): the floor is the dependency chain, about 16 clk per step"}
+    del X, y, resid, vol
+    rows_c3, F, ph = N_STOCKS * (C3_MONTHS + 13), 115, P_FEAT // 2
+    Xf = torch.rand(rows_c3, F, dtype=torch.float64, device=dev, generator=g)
+    W = 0.22 * torch.randn(F, ph, dtype=torch.float64, device=dev, generator=g)
+    o = torch.empty(rows_c3, 2 * ph, dtype=torch.float64, device=dev)
+    ms = timed(lambda: lib.pfml_rff_sincos(ptr(Xf), ptr(W), rows_c3, F, ph, ptr(o), st))
+    by = rows_c3 * (F + 2 * ph) * 8
+    out["a1_rff_sincos"] = {"ms": ms, "algorithmic_bytes": by, "gbs": by / ms * 1e-6, "frac_of_hbm_peak": by / ms * 1e-6 / hbm,
+                            "rows": rows_c3, "flops": 2.0 * rows_c3 * F * ph, "tflops": 2.0 * rows_c3 * F * ph / ms * 1e-9,
+                            "note": "FP64 GEMM (K = 115) with a sincos epilogue: 1.53 GB written; the FP64 sin/cos of the epilogue, not "
+                                    "HBM, paces it"}
+    return out
 
 
 def measure_fp64_peak(torch, dev):
@@ -280,12 +417,35 @@ def run_ours(args, rank, world, local_rank):
                           "executed_tflops": 2.0 * B * NP * P * NP / ms * 1e-9, "rel_err_vs_cublas": err}))
         return
 
-    # ---- value: inputs resident in HBM -------------------------------------------------------------
+    # ---- the step: B date-steps with the window sums fused in, then (N > 1) the all-reduce of the sums ----------
+    sc = importlib.import_module(PKG + ".pfml_search_coef")
+    comm_mod = importlib.import_module(PKG + ".comm")
+    comm = comm_mod.Communicator.from_torch_distributed(device=dev) if world > 1 else None
+    me = panel.month_ends[months]
+    y0 = int(str(me[0])[:4])
+    hp_years = list(range(y0 + 2, int(str(me[-1])[:4]) + 2))          # burn-in = first calendar year; every date lies in a window
+    bucket_np = sc.rank_buckets(me, hp_years)
+    assert (bucket_np >= 0).all()
+    nbk = len(hp_years) + 1
+    bucket = torch.as_tensor(bucket_np.astype(np.int32)).to(dev)
+    Pn = P_FEAT + 1
+    r_sum = torch.zeros((nbk, Pn), dtype=torch.float64, device=dev)
+    d_sum = torch.zeros((nbk, Pn, Pn), dtype=torch.float64, device=dev)
+    cnt = torch.as_tensor(np.bincount(bucket_np, minlength=nbk).astype(np.float64)).to(dev)
+    cnt_step = cnt.clone()
+    allreduce_bytes = int(r_sum.numel() + d_sum.numel() + cnt.numel()) * 8 if world > 1 else 0
+
+    def step():
+        r_sum.zero_(); d_sum.zero_(); cnt_step.copy_(cnt)
+        runner.run_bucketed(bucket, nbk, r_sum, d_sum)
+        if comm is not None:
+            comm.allreduce_sums(r_sum, d_sum, cnt_step)
+
     for _ in range(args.warmup):
-        runner.run()
+        step()
     if args.profile_only:
         for _ in range(args.steps):
-            runner.run()
+            step()
         torch.cuda.synchronize(dev)
         print(json.dumps({"profile_only": True, "dates": B, "steps": args.steps, "launches_per_step":
                           lib.pfml_launch_count() // (args.warmup + args.steps)}))
@@ -296,7 +456,7 @@ def run_ours(args, rank, world, local_rank):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        runner.run()
+        step()
     e1.record()
     barrier()
     launches = lib.pfml_launch_count() - l0
@@ -307,15 +467,33 @@ def run_ours(args, rank, world, local_rank):
     ms_total = float(ms.item())
     value = world * B * args.steps / (ms_total * 1e-3)
     assert int(runner.status.abs().sum().item()) == 0, "numerical failure flag set"
+    # the fused sums against a separate pass over the outputs (bit-exact), and the all-reduced count
+    r_chk, d_chk = sc.bucket_sums(runner.r_tilde, runner.denom, bucket_np, nbk)
+    if world == 1:
+        assert torch.equal(d_chk, d_sum) and torch.equal(r_chk, r_sum), "fused window sums differ from the separate pass"
+    assert float(cnt_step.sum().item()) == world * B
+    # the all-reduce alone (same buffers), for the record
+    ar_ms = None
+    if comm is not None:
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(5):
+            comm.allreduce_sums(r_sum, d_sum, cnt_step)
+        a1.record()
+        barrier()
+        t = torch.tensor([a0.elapsed_time(a1) / 5], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ar_ms = float(t.item())
 
     # ---- the opt-in 6-digit mode of the INT8 path (pfml_set_emulation(2)), same steps: reported beside the default ----
     lib.pfml_set_emulation(2)
-    runner.run()
+    step()
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
     for _ in range(args.steps):
-        runner.run()
+        step()
     f1.record()
     barrier()
     lib.pfml_set_emulation(1)
@@ -329,69 +507,78 @@ def run_ours(args, rank, world, local_rank):
     pms, pfl, pln = (np.zeros(nt) for _ in range(3))
     lib.pfml_prof_enable(1)
     for _ in range(args.steps):
-        runner.run()
+        runner.run_bucketed(bucket, nbk, r_sum, d_sum)
     lib.pfml_prof_collect(C.c_void_p(pms.ctypes.data), C.c_void_p(pfl.ctypes.data), C.c_void_p(pln.ctypes.data))
     lib.pfml_prof_enable(0)
     names = [lib.pfml_prof_tag_name(i).decode() for i in range(nt)]
+    resident_ref = {k: getattr(runner, k)[0].cpu().numpy() for k in ("risk", "tc", "denom")}
+    ws_gb = runner.ws_bytes / 1e9
 
-    # ---- e2e: host buffers in / out through pfml_date_steps_host ------------------------------------
+    # ---- e2e: host buffers in / out through pfml_date_steps_host_packed ---------------------------------
     # pinned host buffers are placed on the NUMA node of the allocating thread: bind it to the GPU's node while they are
     # allocated (with 8 ranks the downloads otherwise cross the socket link), then give the affinity back
     numa = bind_to_gpu_numa(torch, dev)
     blk = host_mod.HostBlock(panel, months, pin=True)
     if numa is not None:
         os.sched_setaffinity(0, numa["before"])
-    for _ in range(max(1, min(args.warmup, 2))):
-        blk.run(chunk=args.chunk, device=local_rank)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        blk.run(chunk=args.chunk, device=local_rank)
-    torch.cuda.synchronize(dev)
-    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-    e2e_val = world * B * args.steps / float(dt.item())
-    assert int(blk.status.abs().sum()) == 0
-    # the same call asking only for the two outputs the metric names (r_tilde, denom): 8.4 MB per date instead of 29
-    blk.run(chunk=args.chunk, device=local_rank, full_outputs=False)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        blk.run(chunk=args.chunk, device=local_rank, full_outputs=False)
-    torch.cuda.synchronize(dev)
-    dt2 = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(dt2, op=dist.ReduceOp.MAX)
-    e2e_two = world * B * args.steps / float(dt2.item())
-    chk = float(np.max(np.abs(blk.out["denom"][0].numpy() - runner.denom[0].cpu().numpy())))
 
+    def e2e_rate(fn):
+        for _ in range(max(1, min(args.warmup, 2))):
+            fn()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            fn()
+        torch.cuda.synchronize(dev)
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        assert int(blk.status.abs().sum()) == 0
+        return world * B * args.steps / float(dt.item())
+
+    e2e_val = e2e_rate(lambda: blk.run_packed(chunk=args.chunk, device=local_rank))
+    risk0, tc0, den0 = blk.unpack(0)
+    chk = max(float(np.max(np.abs(risk0 - resident_ref["risk"]))), float(np.max(np.abs(tc0 - resident_ref["tc"]))),
+              float(np.max(np.abs(den0 - resident_ref["denom"]))))
+    e2e_full = e2e_rate(lambda: blk.run(chunk=args.chunk, device=local_rank))
+    chk_full = float(np.max(np.abs(blk.out["denom"][0].numpy() - resident_ref["denom"])))
+    e2e_two = e2e_rate(lambda: blk.run(chunk=args.chunk, device=local_rank, full_outputs=False))
+    h2d_bytes, d2h_packed, d2h_full = int(blk.h2d_bytes), int(blk.d2h_bytes), int(blk.d2h_bytes_full_squares)
+    del blk, runner, dpanel
+    torch.cuda.empty_cache()
+
+    # ---- hp-grid wall-time: the whole C3 + C4 pipeline at N GPUs (all ranks take part) ---------------------
+    hp = hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, B) if not args.no_hp_grid else None
+    if comm is not None:
+        comm.close()
     if rank != 0:
         return
     # ---- roofline of the dominant kernel ---------------------------------------------------------------
-    # The dominant kernel is pfml::emu_gemm_kernel: the n x n x P products of the Horner / solve steps (14 launches per
-    # step) and the n x n x n chain products (11 launches) as FP64-equivalent GEMMs on the INT8 tensor cores.  Its
-    # duration is measured live with CUDA events around every launch (library profiling slot `emu_i8_gemm`), the
-    # algorithmic work is 2 M N K FP64 flops per product.  One FP64-equivalent product costs 28 int8 slice products,
-    # so the tensor-pipe ceiling in FP64-equivalent flops is (INT8 dense peak) / 28; the INT8 dense peak is taken as
-    # 2 x the measured bf16 GEMM peak of MEASURED_PEAKS.json (sustained figure: the kernel is timed inside a long step).
+    # pfml::emu_gemm_kernel: the n x n x P products of the sums / solves (14 launches per step), the n x n x n chain
+    # products (11) and the two symmetric a9 contractions as FP64-equivalent GEMMs on the INT8 tensor cores.  Duration:
+    # CUDA events around every launch (library profiling slot `emu_i8_gemm`) over the timed steps.  Work: SURVEY 8(d)'s
+    # algorithmic flops (n = 500, not the padded 512; n P^2 per symmetric launch).  Ceiling: the INT8 tensor pipe MEASURED
+    # here with back-to-back tcgen05.mma.kind::i8 (pfml_int8_mma_probe), divided by the 28 digit products per FP64 product.
     peak_fp64 = measure_fp64_peak(torch, dev)
+    probe = {}
+    for nm, n_, ts in (("pipe_peak_M128_N256_A_in_TMEM", 256, 1), ("N256_SS", 256, 0), ("kernel_shape_N64_A_in_TMEM", 64, 1),
+                       ("kernel_shape_N64_SS", 64, 0)):
+        tops, clk = C.c_double(), C.c_double()
+        rc = lib.pfml_int8_mma_probe(n_, 8192, ts, C.byref(tops), C.byref(clk))
+        probe[nm] = {"tops": tops.value, "nominal_clk_per_mma": clk.value} if rc == 0 else {"error": rc}
+    int8_peak = probe["pipe_peak_M128_N256_A_in_TMEM"].get("tops", 0.0)
+    n_pairs = 28
+    # the kernel's own instruction mix per 32-byte k slab: 18 products with A in TMEM, 10 with both operands in shared memory
+    mix = None
+    if "tops" in probe["kernel_shape_N64_A_in_TMEM"] and "tops" in probe["kernel_shape_N64_SS"]:
+        mix = 28.0 / (18.0 / probe["kernel_shape_N64_A_in_TMEM"]["tops"] + 10.0 / probe["kernel_shape_N64_SS"]["tops"])
     off = official_flops_per_date()
     k_emu = names.index("emu_i8_gemm")
     emu_ms = pms[k_emu] / args.steps
     emu_launches = pln[k_emu] / args.steps
-    emu_flops = pfl[k_emu] / args.steps
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        bf16_peak = float(json.load(open(peaks_path)).get("bf16_tflops_sustained", 1400.0))
-        peak_src = "2 x bf16_tflops_sustained of MEASURED_PEAKS.json (%.1f) / 28 slice products, of measured" % bf16_peak
-    else:
-        bf16_peak = 1400.0
-        peak_src = "2 x 1400 TFLOP/s (sustained bf16 fallback of B200_PROFILING.md) / 28 slice products, of fallback"
-    n_pairs = 28
-    peak = 2.0 * bf16_peak / n_pairs
-    achieved = emu_flops / (emu_ms * 1e-3) * 1e-12 if emu_ms > 0 else 0.0
-    horner_ms = pms[4] / args.steps
+    emu_alg = algorithmic_flops_emu_per_date() * B
+    peak = int8_peak / n_pairs if int8_peak > 0 else None
+    achieved = emu_alg / (emu_ms * 1e-3) * 1e-12 if emu_ms > 0 else 0.0
     gemm_ms = pms[0] / args.steps                      # all DMMA GEMM launches of one step
     total_stage_ms = sum(pms[1:7]) / args.steps
     traffic = None
@@ -402,50 +589,77 @@ def run_ours(args, rank, world, local_rank):
             traffic = per_date * B if per_date else None
         except Exception:
             traffic = None
-    stage_map = {"m_func": off["m_func"], "chain_nxn": 22 * N_STOCKS ** 3, "horner_nxP": 24 * N_STOCKS ** 2 * (P_FEAT + 1),
-                 "solve": off["solve"], "denom": off["denom"]}
+    n, P = N_STOCKS, P_FEAT + 1
+    stage_map = {"m_func": off["m_func"], "chain_nxn": 22 * n ** 3, "horner_nxP": 24 * n * n * P, "solve": off["solve"], "denom": off["denom"]}
     stages = {}
     for i in range(1, 7):
         st_ms = pms[i] / args.steps
         stages[names[i]] = {"ms_per_step": round(st_ms, 3), "share": round(st_ms / total_stage_ms, 4)}
         if names[i] in stage_map:
-            stages[names[i]]["algorithmic_tflops"] = round(stage_map[names[i]] * B / (st_ms * 1e-3) * 1e-12, 2)
-    hp = hp_grid_walltime(torch, dev, runner, B)
+            tf = stage_map[names[i]] * B / (st_ms * 1e-3) * 1e-12
+            stages[names[i]]["algorithmic_tflops"] = round(tf, 2)
+            stages[names[i]]["vs_cublas_dgemm_peak"] = round(tf / peak_fp64, 3)
+    if peak:
+        stages["denom"]["roofline"] = {"bound": "tensor", "achieved": stages["denom"]["algorithmic_tflops"], "peak": peak,
+                                       "unit": "TFLOP/s", "frac": stages["denom"]["algorithmic_tflops"] / peak,
+                                       "note": "whole a9 stage (graded contraction): stacked factor GEMMs on the DMMA pipe, two symmetric "
+                                               "INT8 contractions, their operand slicing and the finish kernel with the fused window sums"}
+    hb = hbm_rows(torch, dev, lib) if world == 1 else None
     cpu_v, cpu_n, cpu_dt = cpu_dates_per_sec(syn)
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "PFML date-step N=500 p=1024 (P=1025), lb=11, 10 m_func iterations (BASELINE configs[2] at the metric's p)",
-                   "dates_per_step_per_gpu": B, "parallelism": f"dates sharded over {world} GPU(s), no data-path collective",
-                   "l2": "per-step working set ~%.1f GB >> 126 MB L2 (inputs larger than L2)" % (runner.ws_bytes / 1e9)},
+        "config": {"workload": WORKLOAD},
+        "details": {"dates_per_step_per_gpu": B,
+                    "step": "B date-steps with the expanding-window sums fused into the a9 finish kernel"
+                            + (f", then one FP64 NCCL all-reduce of the [{nbk}] x (P + P^2 + 1) sums over {world} ranks "
+                               f"({allreduce_bytes} bytes per rank per step)" if world > 1 else " (one rank: no exchange)"),
+                    "parallelism": f"dates sharded over {world} GPU(s); collective in the timed region: "
+                                   + ("pfml_comm_allreduce_sums (NCCL, FP64 sum)" if world > 1 else "none at N = 1"),
+                    "allreduce_ms_alone": ar_ms, "allreduce_bytes_per_step": allreduce_bytes,
+                    "l2": "per-step working set ~%.1f GB >> 126 MB L2 (inputs larger than L2)" % ws_gb},
         "clocks": clocks,
         "value_six_digit_mode": {"value": value_six, "unit": UNIT,
                                  "note": "pfml_set_emulation(2): 6 of 7 digits for the non-compounding products; 7e-12 of the "
                                          "DMMA result instead of 1e-13 (tolerance 1e-8); not the default"},
-        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(blk.h2d_bytes), "d2h_bytes_per_step": int(blk.d2h_bytes),
-                "outputs": "r_tilde, denom, risk, tc, signal_t (everything PFML_Input_Data.py stores per date)",
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_packed,
+                "entry_point": "pfml_date_steps_host_packed",
+                "outputs": "r_tilde, signal_t and the upper triangles of risk and tc (denom = risk + tc exactly; all three symmetric): "
+                           "everything PFML_Input_Data.py stores per date, without the redundant two thirds of the squares",
                 "chunk": args.chunk, "max_abs_diff_vs_resident_path": chk,
-                "value_r_tilde_denom_only": e2e_two, "d2h_bytes_per_step_r_tilde_denom_only": int(B * (P_FEAT + 1) * (P_FEAT + 2) * 8),
+                "value_full_squares": e2e_full, "d2h_bytes_per_step_full_squares": d2h_full,
+                "max_abs_diff_vs_resident_path_full_squares": chk_full,
+                "value_r_tilde_denom_only": e2e_two,
                 "host_buffers": "pinned, allocated on the GPU's NUMA node" if numa else "pinned"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor",
                      "kernel": "pfml::emu_gemm_kernel (tcgen05.mma kind::i8, TMEM accumulators, bulk-TMA operands): FP64-equivalent "
-                               "batched products [512 x 1025 x 512] (Horner, solves) and [512 x 512 x 512] (chain)",
-                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                               "batched products [500 x 1025 x 500] (sums, solves), [500 x 500 x 500] (chain) and the symmetric "
+                               "[1025 x 1025 x 500] a9 contractions (upper triangle)",
+                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if peak else None, "traffic": traffic,
                      "traffic_note": "DRAM bytes of one n x P launch (ncu --set full, profiles/ncu_summary.json)",
-                     "flop_kind": "FP64-equivalent (algorithmic 2 M N K per product); executed INT8 rate = 28 x achieved x padding",
-                     "peak_source": peak_src,
-                     "executed_int8_tops": achieved * n_pairs * (1088.0 / 1025.0),
+                     "flop_kind": "FP64-equivalent, SURVEY 8(d) algorithmic flops: (22 n^3 + 28 n^2 P + 2 n P^2) per date at n = 500, "
+                                  "P = 1025 = 10.98 GFLOP; executed INT8 rate = 28 x achieved x padding",
+                     "peak_source": "measured in this run: pfml_int8_mma_probe, back-to-back tcgen05.mma.kind::i8 M=128 N=256 K=32 with A "
+                                    "in TMEM on all SMs (%.0f TOPS) / 28 digit products per FP64 product" % int8_peak,
+                     "int8_probe": probe,
+                     "frac_of_instruction_mix_ceiling": (achieved * n_pairs / mix) if mix else None,
+                     "instruction_mix_ceiling_note": "the kernel issues M=128 N=64 K=32 (7 int32 accumulators x 64 columns fill TMEM): "
+                                                     "18 products per k slab with A in TMEM, 10 from shared memory; harmonic mean of the "
+                                                     "two probed rates = %s TOPS" % (("%.0f" % mix) if mix else "n/a"),
                      "vs_cublas_dgemm_peak": achieved / peak_fp64, "cublas_dgemm_peak_tflops": peak_fp64,
-                     "algorithmic_flops_per_step": emu_flops, "launch_ms_avg": emu_ms / max(emu_launches, 1.0),
+                     "algorithmic_flops_per_step": emu_alg, "executed_padded_flops_per_step": pfl[k_emu] / args.steps,
+                     "launch_ms_avg": emu_ms / max(emu_launches, 1.0),
                      "launches_per_step": emu_launches, "share_of_step": emu_ms / (ms_total / args.steps),
                      "dmma_gemm_launches": {"executed_tflops": pfl[0] / args.steps / (gemm_ms * 1e-3) * 1e-12,
                                             "ms_per_step": gemm_ms, "launches_per_step": pln[0] / args.steps,
                                             "share_of_step": gemm_ms / (ms_total / args.steps),
                                             "peak": peak_fp64, "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, best of 5, this run"},
-                     "algorithmic_flops_per_date": off["total"]},
+                     "algorithmic_flops_per_date": off["total"],
+                     "whole_step_algorithmic_tflops": off["total"] * B / (ms_total / args.steps * 1e-3) * 1e-12},
         "hp_grid": hp,
+        "hbm_rows": hb,
         "stages": stages,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                          "sample": f"{cpu_n} date-steps of the same N=500, p=1024 workload in {cpu_dt:.1f} s (numpy oracle, all host BLAS threads)"},
@@ -479,6 +693,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=0, help="dates per device chunk in the host entry point (0 = library schedule)")
     ap.add_argument("--profile-only", action="store_true", help="resident-path steps only (for ncu launch lists)")
     ap.add_argument("--gemm-only", action="store_true", help="the dominant GEMM shape alone (for ncu --set full)")
+    ap.add_argument("--no-hp-grid", action="store_true", help="skip the C3 + C4 pipeline wall-time")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -494,6 +709,9 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     try:
         run_ours(args, rank, world, local_rank)
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()                      # rank 0 still times the CPU arm after the other ranks are done
     finally:
         if world > 1:
             import torch.distributed as dist

@@ -295,6 +295,13 @@ int pfml_date_steps_host_packed(const pfml_host_block_t* blk, int B, int n_max, 
 int pfml_unpack_upper(const double* ut, int P, double* full);
 int pfml_unpack_reals(const double* risk_ut, const double* tc_ut, int P, double* risk, double* tc, double* denom);
 
+/* Measured ceiling of the INT8 tensor pipe for one instruction shape (no reference counterpart; bench.py prints it beside
+ * the achieved rate of the emulated GEMM): `iters` back-to-back tcgen05.mma.kind::i8 of M = 128, N = n, K = 32 per SM on
+ * operands resident in shared memory (ts_form = 0) or with A in TMEM (ts_form = 1), accumulators in TMEM, nothing else.
+ * tops = 1e-12 * int8 multiply-adds * 2 per second over all SMs; clk_per_mma (may be NULL) at the nominal maximum SM
+ * clock.  Allocates one int on the device; synchronises. */
+int pfml_int8_mma_probe(int n, int iters, int ts_form, double* tops, double* clk_per_mma);
+
 /* Device-time accounting with CUDA events (used by bench.py for the live roofline): enable, run, collect.
  * pfml_prof_collect synchronises the device, fills ms/flops/launches [n_tags] and clears the log.
  * Tag 0 = all DMMA GEMM launches; tags 1.. = pipeline stages (see pfml_prof_tag_name). */

