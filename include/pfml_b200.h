@@ -295,6 +295,13 @@ int pfml_date_steps_host_packed(const pfml_host_block_t* blk, int B, int n_max, 
 int pfml_unpack_upper(const double* ut, int P, double* full);
 int pfml_unpack_reals(const double* risk_ut, const double* tc_ut, int P, double* risk, double* tc, double* denom);
 
+/* f4 -- cross-sectional percentile ranks of the characteristics, Prepare_Data.py:338-345 (+ the 0.5 imputation of :368
+ * when impute_half != 0): X [T][N][F] dense, NaN = missing value / absent row; out [T][N][F] (may alias X only if the
+ * caller does not need X).  Per (month, characteristic): pandas' groupby('eom').rank(pct=True) -- average rank of ties
+ * over the count of non-missing values --, exact zeros put back to 0, missing -> 0.5 or NaN.  Bit-identical to pandas
+ * (integer ranks, one FP64 division).  N <= 4096 rows per month. */
+int pfml_percentile_rank(const double* X, int T, int N, int F, int impute_half, double* out, void* stream);
+
 /* Measured ceiling of the INT8 tensor pipe for one instruction shape (no reference counterpart; bench.py prints it beside
  * the achieved rate of the emulated GEMM): `iters` back-to-back tcgen05.mma.kind::i8 of M = 128, N = n, K = 32 per SM on
  * operands resident in shared memory (ts_form = 0) or with A in TMEM (ts_form = 1), accumulators in TMEM, nothing else.

@@ -179,8 +179,9 @@ def denom_sum_fun(train):
     return d_sum[0].cpu().numpy()
 
 
-def run(path, settings=None, device="cuda:0"):
-    """PFML_Search_Coef.py: reads Data/pfml_input_{g}.pkl, writes Data/coef_dict_{g}.pkl (:60-143), same schema
+def run(path, settings=None, device="cuda:0", source="pickle"):
+    """PFML_Search_Coef.py: reads Data/pfml_input_{g}.pkl (or, with source="store", the dense tensor store written by
+    pfml_input_data.run_store), writes Data/coef_dict_{g}.pkl (:60-143), same schema
     ``{g: {year: {p: {lambda_index: Series}}}}``."""
     import os
     import pickle
@@ -193,12 +194,17 @@ def run(path, settings=None, device="cuda:0"):
     p_vec, l_vec = settings["pf_ml"]["p_vec"], settings["pf_ml"]["l_vec"]
     out = {}
     for g_index, _g in enumerate(settings["pf_ml"]["g_vec"]):
-        with open(os.path.join(path, "Data", f"pfml_input_{g_index}.pkl"), "rb") as f:
-            reals = pickle.load(f)[g_index]["reals"]
-        d_all = sorted(reals.keys())
-        r_t = np.stack([reals[d]["r_tilde"].to_numpy() for d in d_all])
-        den = np.stack([reals[d]["denom"].to_numpy() for d in d_all])
-        me = np.array([np.datetime64(pd.Timestamp(d).date()) for d in d_all])
+        if source == "store":
+            from .tensor_store import Store
+            st = Store(path, g_index)
+            r_t, den, me = np.array(st.r_tilde), st.denom_stack(), st.dates
+        else:
+            with open(os.path.join(path, "Data", f"pfml_input_{g_index}.pkl"), "rb") as f:
+                reals = pickle.load(f)[g_index]["reals"]
+            d_all = sorted(reals.keys())
+            r_t = np.stack([reals[d]["r_tilde"].to_numpy() for d in d_all])
+            den = np.stack([reals[d]["denom"].to_numpy() for d in d_all])
+            me = np.array([np.datetime64(pd.Timestamp(d).date()) for d in d_all])
         coef = search_coef(r_t, den, me, hp_years, p_vec, l_vec, device=device)
         coef_dict = {int(y): {int(p): {j: pd.Series(coef[int(y)][int(p)][j], index=pfml_feat_fun(int(p))) for j in range(len(l_vec))}
                               for p in p_vec} for y in hp_years}

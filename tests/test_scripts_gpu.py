@@ -101,3 +101,64 @@ def test_function_mirrors(syn):
     r = pkg("pfml_input_data").rff(pn.feats[0], W=pn.W)
     assert relerr(r["X_cos"], np.cos(pn.feats[0] @ pn.W)) < 1e-14 and relerr(r["X_sin"], np.sin(pn.feats[0] @ pn.W)) < 1e-14
     assert GF.create_lambda({1: 0.1, 2: 0.2, 3: 0.3}, [3, 1]).tolist() == [[0.3, 0.0], [0.0, 0.1]]
+
+
+def test_tensor_store_equals_pickle_outputs(tmp_path, syn):
+    """pfml_input_data.run_store (packed host entry point -> memory-mapped store) holds exactly what run() pickles, and
+    PFML_Search_Coef from the store equals PFML_Search_Coef from the pickle."""
+    z = np.load(os.path.join(GOLD, "pfml_ref_small.npz"))
+    panel = panel_from_golden(z, syn)
+    path = str(tmp_path) + "/"
+    syn.write_reference_artefacts(panel, path)
+    GF = pkg("general_functions")
+    settings, pf_set = GF.get_settings()
+    settings["split"]["test_end"] = pd.Timestamp(panel.month_ends[-1])
+    settings["pf"]["dates"].update(start_year=2013, end_yr=2014)
+    settings["pf_ml"].update(g_vec=[panel.meta["g"]], p_vec=[int(p) for p in z["p_vec"]], l_vec=[float(l) for l in z["l_vec"]])
+    st = (settings, pf_set)
+    ref = pkg("pfml_input_data").run(path, st)[0]
+    dirs = pkg("pfml_input_data").run_store(path, st, block=7)
+    assert os.path.exists(os.path.join(dirs[0], "meta.json"))
+    store = pkg("tensor_store").Store(path, 0)
+    leg = store.to_legacy()
+    assert sorted(leg["reals"].keys()) == sorted(ref["reals"].keys())
+    for d in ref["reals"]:
+        for name in ("r_tilde", "denom", "risk", "tc"):
+            a, b = leg["reals"][d][name], ref["reals"][d][name]
+            assert np.array_equal(a.to_numpy(), b.to_numpy()), (d, name)
+            assert list(a.index) == list(b.index)
+        assert leg["signal_t"][d].equals(ref["signal_t"][d])
+    assert np.array_equal(leg["rff_w"], ref["rff_w"])
+    size_store = sum(os.path.getsize(os.path.join(dirs[0], f)) for f in os.listdir(dirs[0]))
+    assert size_store < os.path.getsize(os.path.join(path, "Data", "pfml_input_0.pkl"))
+    c_pkl = pkg("pfml_search_coef").run(path, st)[0]
+    c_sto = pkg("pfml_search_coef").run(path, st, source="store")[0]
+    for y in c_pkl:
+        for p in c_pkl[y]:
+            for j in c_pkl[y][p]:
+                assert np.array_equal(c_pkl[y][p][j].to_numpy(), c_sto[y][p][j].to_numpy())
+
+
+def test_percentile_rank_bit_exact_vs_pandas():
+    """pfml_percentile_rank vs the reference's own three lines (Prepare_Data.py:338-345, :368): ties, zeros, NaNs, a month
+    with a single non-missing value, an all-missing column."""
+    rng = np.random.default_rng(9)
+    T, N, F = 5, 300, 7
+    x = np.round(rng.standard_normal((T, N, F)), 1)              # one decimal: many ties
+    x[rng.random((T, N, F)) < 0.1] = np.nan
+    x[rng.random((T, N, F)) < 0.05] = 0.0
+    x[1, :, 2] = np.nan; x[1, 17, 2] = 3.0                       # single value
+    x[2, :, 4] = np.nan                                          # nothing to rank
+    x[3, 5, 0] = np.inf; x[3, 6, 0] = -np.inf
+    got = pkg("prepare_data").percentile_rank(x, impute=True)
+    got_nan = pkg("prepare_data").percentile_rank(x, impute=False)
+    feats = [f"f{k}" for k in range(F)]
+    chars = pd.DataFrame(x.reshape(T * N, F), columns=feats)
+    chars["eom"] = np.repeat(np.arange(T), N)
+    ranked = chars.groupby("eom")[feats].rank(pct=True)
+    mask = chars[feats] == 0.0
+    ranked[mask] = 0
+    want_nan = ranked.to_numpy().reshape(T, N, F)
+    want = ranked.apply(lambda c: c.fillna(0.5)).to_numpy().reshape(T, N, F)
+    assert np.array_equal(got, want)
+    assert np.array_equal(got_nan, want_nan, equal_nan=True)
