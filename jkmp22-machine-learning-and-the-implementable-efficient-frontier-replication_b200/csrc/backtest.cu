@@ -149,7 +149,12 @@ backtest_kernel(int B, int NP, int N, const double* __restrict__ m, const double
     for (int i = tid; i < N; i += blockDim.x) carry[i] = 0.0;
     __syncthreads();
     const double mu1 = mu_ld1[t];
-    for (int i = tid; i < n; i += blockDim.x) carry[sl[i]] = wn[i] * (1.0 + tr_ld1[row0 + sl[i]]) / (1.0 + mu1);
+    // a NaN drifted weight (missing tr_ld1 / mu_ld1) is not carried: the reference writes w_opt_ld1 into next month's
+    // w_start and then sets every NaN w_start to 0 (PFML_best_hps.py:204-210)
+    for (int i = tid; i < n; i += blockDim.x) {
+      const double v = wn[i] * (1.0 + tr_ld1[row0 + sl[i]]) / (1.0 + mu1);
+      carry[sl[i]] = isnan(v) ? 0.0 : v;
+    }
     __syncthreads();
   }
 }

@@ -111,6 +111,18 @@ def ewma_vol(x, lam, start, device="cuda:0"):
     return ewma_vol_batch([x], lam, start, device)[0]
 
 
+def ewma_wrapper(series, settings=None, device="cuda:0"):
+    """"Estimate Covariance Matrix.py":389-397: Series -> ewma_vol with lam = 0.5 ** (1 / hl_stock_var) and
+    start = initial_var_obs from ``settings['cov_set']`` (the reference reads the global ``settings``; here it is an
+    argument that defaults to ``get_settings()``) -> Series on the same index.  For many stocks use ewma_vol_batch: one launch."""
+    import pandas as pd
+
+    from . import general_functions as GF
+    cs = (settings or GF.get_settings()[0])["cov_set"]
+    out = ewma_vol(series.values.astype(float), 0.5 ** (1 / cs["hl_stock_var"]), cs["initial_var_obs"], device)
+    return pd.Series(out, index=series.index)
+
+
 # ------------------------------------------------------------------------------------------------------
 # script-level drop-in
 # ------------------------------------------------------------------------------------------------------

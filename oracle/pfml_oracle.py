@@ -348,6 +348,7 @@ def pfml_w(panel, dates_idx, w_aim, vol_scale=None):
             for j, i in enumerate(sel):
                 if int(i) in pos:
                     w_start[j] = prev[1][pos[int(i)]]
+            w_start = np.nan_to_num(w_start, nan=0.0)                               # :210: NaN w_start (NaN tr_ld1 / mu_ld1) -> 0
         sigma = create_cov(panel.fct_load[t][sel], panel.fct_cov[t], panel.ivol[t, sel])
         m = m_func(panel.wealth[t], panel.mu, panel.rf[t], sigma * panel.gamma_rel, panel.gamma_rel,
                    create_lambda(panel.lam[t, sel]), panel.iterations)               # :186-190

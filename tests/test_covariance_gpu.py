@@ -79,3 +79,18 @@ def test_ewma_vol_golden_and_edge_cases():
     assert np.isnan(out[1]).all() and np.isnan(out[2]).all()
     o3 = O.ewma_vol(other, lam, 63)
     assert np.nanmax(np.abs(out[3] - o3) / o3) < 1e-15
+
+
+def test_ewma_wrapper_mirror():
+    """Same-named drop-in of "Estimate Covariance Matrix.py":389-397: Series in, Series out, settings-driven lam / start."""
+    import pandas as pd
+    ec = pkg("estimate_covariance")
+    GF = pkg("general_functions")
+    settings, _ = GF.get_settings()
+    rng = np.random.default_rng(12)
+    s = pd.Series(0.01 * rng.standard_normal(400), index=pd.date_range("2020-01-01", periods=400, freq="B"))
+    s.iloc[[70, 71, 200]] = np.nan
+    got = ec.ewma_wrapper(s, settings)
+    ref = O.ewma_vol(s.values.astype(float), 0.5 ** (1 / settings["cov_set"]["hl_stock_var"]), settings["cov_set"]["initial_var_obs"])
+    assert got.index.equals(s.index)
+    assert np.allclose(got.to_numpy(), ref, rtol=1e-13, atol=0, equal_nan=True)

@@ -69,3 +69,21 @@ def test_aim_and_backtest(gold, syn):
     sig = O.create_cov(panel.fct_load[t][sel], panel.fct_cov[t], panel.ivol[t, sel])
     m_ref = O.m_func(panel.wealth[t], panel.mu, panel.rf[t], sig * panel.gamma_rel, panel.gamma_rel, np.diag(panel.lam[t, sel]), 10)
     assert relerr(res["m"][3, :len(sel), :len(sel)].cpu().numpy(), m_ref) < 1e-8
+
+
+def test_backtest_nan_drift_starts_at_zero(syn):
+    """A missing tr_ld1 for a held stock: the reference writes the NaN drifted weight into next month's w_start and then
+    sets NaN w_start to 0 (PFML_best_hps.py:199-210), so the stock restarts at 0 and nothing else is contaminated."""
+    panel = syn.make_panel(N=60, T=20, p=8, seed=81, ragged=0.05)
+    oos = [13, 14, 15, 16]
+    rng = np.random.default_rng(82)
+    w_aim = [rng.standard_normal(int(panel.valid[t].sum())) * 0.01 for t in oos]
+    held = np.flatnonzero(panel.valid[13] & panel.valid[14])[4]
+    panel.tr_ld1[13, held] = np.nan
+    ref = O.pfml_w(panel, oos, {t: w for t, w in zip(oos, w_aim)})
+    res = pkg("pfml_best_hps").pfml_w(panel, oos, w_aim)
+    for b, t in enumerate(oos):
+        assert np.isfinite(res["w"][b]).all() and np.isfinite(res["w_start"][b]).all()
+        assert relerr(res["w_start"][b], ref[t]["w_start"]) < 1e-8 and relerr(res["w"][b], ref[t]["w"]) < 1e-8
+    j = list(np.flatnonzero(panel.valid[14])).index(held)
+    assert res["w_start"][1][j] == 0.0
