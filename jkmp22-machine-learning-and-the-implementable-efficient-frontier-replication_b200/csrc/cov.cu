@@ -16,60 +16,111 @@ namespace {
 constexpr int KC = 32;   // factors padded (K <= 32)
 
 // ---- a15: one CTA per day -------------------------------------------------------------------------
-// Rows of day d are [day_ptr[d], day_ptr[d+1]).  X'X and X'y are accumulated from 64-row chunks staged in shared
-// memory; the K x K system is solved by Cholesky.  A pivot that is zero relative to the largest diagonal entry
-// (an industry without any stock that day gives an exactly zero row/column, the case in which the reference's
-// np.linalg.solve raises and it falls back to pinv, :226-229) drops that factor: its coefficient is 0, which is
-// what pinv returns for a zero row/column; status bit 0 records the fallback.
+// Rows of day d are [day_ptr[d], day_ptr[d+1]).  The day's rows [x_1 .. x_K, y] are streamed through shared memory in
+// chunks of 128 rows (coalesced flat copies of X, row stride padded to 28 doubles so that four consecutive columns are
+// one 16-byte-aligned pair of loads).  The augmented Gram matrix [X y]'[X y] is formed in 4 x 4 register tiles: the 28
+// lower-triangle tiles of the 7 x 7 tile grid go to 28 lanes of every warp, warp w takes the rows i = w (mod 4) of the
+// chunk -- four 16-byte loads feed sixteen FMAs, where one accumulator per thread needed two loads per FMA and was bound
+// by shared-memory bandwidth.  The four partial matrices are added in warp order (deterministic).  The K x K system is
+// solved by a warp: Cholesky, then forward / backward substitution with one lane per unknown.  A pivot that is zero
+// relative to the largest diagonal entry (an industry without any stock that day gives an exactly zero row / column, the
+// case in which the reference's np.linalg.solve raises and it falls back to pinv, :226-229) drops that factor: its
+// coefficient is 0, which is what pinv returns for a zero row / column; status bit 0 records the fallback.  The residual
+// pass streams the rows a second time (L2 hits: a day is 100 KB) with one thread per row.
+constexpr int KA = 28;   // padded width of an augmented row [x (K <= 27) | y | 0..]
+
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 __global__ void __launch_bounds__(128)
 xs_ols_kernel(int K, const double* __restrict__ X, const double* __restrict__ y, const long* __restrict__ day_ptr,
               double* __restrict__ coef, double* __restrict__ resid, int* __restrict__ status) {
   constexpr int CH = 64, S = KC + 1;
+  __shared__ __align__(16) double Xc[2][CH * KA];  // two chunks of augmented rows: the next one loads while this one is used
   __shared__ double A[KC][S];
-  __shared__ double rhs[KC];
-  __shared__ double Xc[CH][S];
-  __shared__ double yc[CH];
-  __shared__ double beta[KC];
+  __shared__ double rhs[KC], beta[KC];
   __shared__ int dropped[KC];
-  const int d = blockIdx.x, tid = threadIdx.x;
+  const int d = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long r0 = day_ptr[d], r1 = day_ptr[d + 1];
-  double acc[8];
+  const int n_chunks = (int)((r1 - r0 + CH - 1) / CH);
+  // lane -> lower-triangle tile (ta >= tc) of the 7 x 7 grid
+  int ta = 0, tc = 0;
+  {
+    int l = lane;
+    while (l > ta) { l -= ta + 1; ta++; }
+    tc = l;
+  }
+  const bool active = lane < 28;
+  double acc[4][4];
 #pragma unroll
-  for (int q = 0; q < 8; q++) acc[q] = 0.0;
-  double accy = 0.0;
-  for (long i0 = r0; i0 < r1; i0 += CH) {
+  for (int u = 0; u < 4; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) acc[u][v] = 0.0;
+  const float invK = 1.0f / (float)K;
+  // asynchronous copies (8 bytes each, many in flight per thread, no registers held): chunk `ck` of the day into buffer `bf`
+  auto load_chunk = [&](int ck, int bf, bool with_y) {
+    const long i0 = r0 + (long)ck * CH;
     const int nr = (int)((r1 - i0) < CH ? (r1 - i0) : CH);
-    __syncthreads();
-    for (int e = tid; e < CH * K; e += 128) {
-      const int r = e / K, c = e % K;
-      Xc[r][c] = r < nr ? X[(i0 + r) * K + c] : 0.0;
+    const double* src = X + i0 * K;
+    for (int e = tid; e < nr * K; e += 128) {
+      const int r = (int)(((float)e + 0.5f) * invK), c = e - r * K;
+      cp_async8(&Xc[bf][r * KA + c], src + e);
     }
-    if (tid < CH) yc[tid] = tid < nr ? y[i0 + tid] : 0.0;
+    if (with_y && tid < nr) cp_async8(&Xc[bf][tid * KA + K], y + i0 + tid);
+    cp_async_commit();
+  };
+  for (int e = tid; e < 2 * CH * KA; e += 128) Xc[0][e] = 0.0;   // the padding columns stay zero (the copies never touch them)
+  __syncthreads();
+  if (n_chunks > 0) load_chunk(0, 0, true);
+  for (int ck = 0; ck < n_chunks; ck++) {
+    const int bf = ck & 1;
+    if (ck + 1 < n_chunks) { load_chunk(ck + 1, bf ^ 1, true); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
+    const long i0 = r0 + (long)ck * CH;
+    const int nr = (int)((r1 - i0) < CH ? (r1 - i0) : CH);
+    if (active) {
+      for (int i = warp; i < nr; i += 4) {
+        const double2* pa = reinterpret_cast<const double2*>(&Xc[bf][i * KA + 4 * ta]);
+        const double2* pc = reinterpret_cast<const double2*>(&Xc[bf][i * KA + 4 * tc]);
+        const double2 a01 = pa[0], a23 = pa[1], c01 = pc[0], c23 = pc[1];
+        const double av[4] = {a01.x, a01.y, a23.x, a23.y}, cv[4] = {c01.x, c01.y, c23.x, c23.y};
 #pragma unroll
-    for (int q = 0; q < 8; q++) {
-      const int e = tid + 128 * q, a = e / KC, c = e % KC;
-      if (a < K && c <= a) {
-        double s = 0.0;
-        for (int i = 0; i < nr; i++) s += Xc[i][a] * Xc[i][c];
-        acc[q] += s;
+        for (int u = 0; u < 4; u++)
+#pragma unroll
+          for (int v = 0; v < 4; v++) acc[u][v] += av[u] * cv[v];
       }
     }
-    if (tid < K) {
-      double s = 0.0;
-      for (int i = 0; i < nr; i++) s += Xc[i][tid] * yc[i];
-      accy += s;
+    __syncthreads();                                        // buffer bf may be overwritten by the load issued next iteration
+  }
+  // the residual pass re-reads the day: start its first chunk now, under the solve (the Gram partials go to buffer 1)
+  static_assert(4 * KA * (KA + 1) <= 2 * CH * KA, "partial Gram matrices fit in the chunk buffers");
+  double* Gp = &Xc[0][0];                                   // [4][KA][KA + 1] over both buffers
+  auto Gat = [&](int w, int r, int c) -> double& { return Gp[(w * KA + r) * (KA + 1) + c]; };
+  if (active) {
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+#pragma unroll
+      for (int v = 0; v < 4; v++) Gat(warp, 4 * ta + u, 4 * tc + v) = acc[u][v];
+  }
+  if (tid < KC) dropped[tid] = 0;
+  __syncthreads();
+  for (int e = tid; e < (K + 1) * KA; e += 128) {          // rows 0 .. K of the augmented matrix, columns <= row
+    const int a = e / KA, c = e % KA;
+    if (c <= a && c < K) {
+      const double v = ((Gat(0, a, c) + Gat(1, a, c)) + Gat(2, a, c)) + Gat(3, a, c);
+      if (a < K) { A[a][c] = v; A[c][a] = v; }
+      else rhs[c] = v;                                       // row K of [X y]'[X y] is X'y
     }
   }
-#pragma unroll
-  for (int q = 0; q < 8; q++) {
-    const int e = tid + 128 * q, a = e / KC, c = e % KC;
-    if (a < K && c <= a) { A[a][c] = acc[q]; A[c][a] = acc[q]; }
-  }
-  if (tid < K) { rhs[tid] = accy; dropped[tid] = 0; }
   __syncthreads();
+  for (int e = tid; e < 2 * CH * KA; e += 128) Xc[0][e] = 0.0;
+  __syncthreads();
+  if (n_chunks > 0) load_chunk(0, 0, false);
   if (tid < 32) {
-    const int r = tid;
+    const int r = lane;
     double dmax = 0.0;
     for (int c = 0; c < K; c++) dmax = fmax(dmax, A[c][c]);
     bool any = false;
@@ -86,28 +137,41 @@ xs_ols_kernel(int K, const double* __restrict__ X, const double* __restrict__ y,
         for (int cc = c + 1; cc <= r; cc++) A[r][cc] -= A[r][c] * A[cc][c];
       __syncwarp();
     }
-    if (r == 0) {
-      // forward then backward substitution (serial: K = 25)
-      for (int i = 0; i < K; i++) {
-        double s = dropped[i] ? 0.0 : rhs[i];
-        for (int a = 0; a < i; a++) s -= A[i][a] * beta[a];
-        beta[i] = dropped[i] ? 0.0 : s / A[i][i];
-      }
-      for (int i = K - 1; i >= 0; i--) {
-        double s = beta[i];
-        for (int a = i + 1; a < K; a++) s -= A[a][i] * beta[a];
-        beta[i] = dropped[i] ? 0.0 : s / A[i][i];
-      }
-      if (any && status) atomicOr(status + d, 1);
+    // forward substitution L z = rhs, then backward L' beta = z: lane r owns unknown r
+    const bool mine = r < K;
+    const bool drop = mine && dropped[r];
+    double sv = (mine && !drop) ? rhs[r] : 0.0;
+    double z = 0.0;
+    for (int i = 0; i < K; i++) {
+      const double zi = __shfl_sync(0xffffffffu, (r == i) ? (drop ? 0.0 : sv / A[r][r]) : 0.0, i);
+      if (r == i) z = zi;
+      if (mine && r > i) sv -= A[r][i] * zi;
     }
+    sv = z;
+    double bt = 0.0;
+    for (int i = K - 1; i >= 0; i--) {
+      const double bi = __shfl_sync(0xffffffffu, (r == i) ? (drop ? 0.0 : sv / A[r][r]) : 0.0, i);
+      if (r == i) bt = bi;
+      if (mine && r < i) sv -= A[i][r] * bi;
+    }
+    if (mine) beta[r] = bt;
+    if (r == 0 && any && status) atomicOr(status + d, 1);
   }
   __syncthreads();
   if (tid < K) coef[(long)d * K + tid] = beta[tid];
-  for (long i = r0 + tid; i < r1; i += 128) {
-    const double* xr = X + i * K;
-    double s = 0.0;
-    for (int c = 0; c < K; c++) s += xr[c] * beta[c];
-    resid[i] = y[i] - s;
+  for (int ck = 0; ck < n_chunks; ck++) {
+    const int bf = ck & 1;
+    if (ck + 1 < n_chunks) { load_chunk(ck + 1, bf ^ 1, false); cp_async_wait<1>(); } else cp_async_wait<0>();
+    __syncthreads();
+    const long i0 = r0 + (long)ck * CH;
+    const int nr = (int)((r1 - i0) < CH ? (r1 - i0) : CH);
+    if (tid < nr) {
+      const double* xr = &Xc[bf][tid * KA];
+      double sacc = 0.0;
+      for (int c = 0; c < K; c++) sacc += xr[c] * beta[c];
+      resid[i0 + tid] = y[i0 + tid] - sacc;
+    }
+    __syncthreads();
   }
 }
 
@@ -200,10 +264,17 @@ wcov_wcor_kernel(int K, int obs, const double* __restrict__ F, const int* __rest
   }
 }
 
-// ---- a17: one thread per stock series ---------------------------------------------------------------
-__global__ void ewma_vol_kernel(int n_series, const double* __restrict__ x, const long* __restrict__ ptr, double lam, int start,
-                                double* __restrict__ vol) {
-  const int sidx = blockIdx.x * blockDim.x + threadIdx.x;
+// ---- a17: one warp per stock series -------------------------------------------------------------------
+// The recurrence var_i = lam var_{i-1} + (1 - lam) x_{i-1}^2 (NaN x: carry) is a 5 000-step dependent chain per series and
+// is evaluated in the reference's order with un-fused multiply and add (numba does not contract), so it cannot be split
+// across lanes without changing the rounding.  What CAN be parallel is everything around it: a warp loads 32 consecutive
+// observations with one coalesced request (the next 32 are already in flight), every lane squares and scales its own
+// observation, then all lanes step through the 32 updates together -- operand j arrives by shuffle, lane j keeps var_j --
+// and the 32 square roots are taken and stored coalesced.  The chain costs two dependent FP64 operations per step;
+// nothing else is on the critical path.
+__global__ void __launch_bounds__(128)
+ewma_vol_kernel(int n_series, const double* __restrict__ x, const long* __restrict__ ptr, double lam, int start, double* __restrict__ vol) {
+  const int sidx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (sidx >= n_series) return;
   const long b0 = ptr[sidx], n = ptr[sidx + 1] - b0;
   const double* xs = x + b0;
@@ -212,23 +283,50 @@ __global__ void ewma_vol_kernel(int n_series, const double* __restrict__ x, cons
   double ss = 0.0;
   int cnt = 0;
   if (n > start) {
-    for (int i = 0; i < start; i++) {
-      const double v = xs[i];
-      if (!isnan(v)) { ss = __dadd_rn(ss, __dmul_rn(v, v)); cnt++; }
+    // initial variance: squares of the first `start` observations summed in order (every lane computes the same sum)
+    for (int i0 = 0; i0 < start; i0 += 32) {
+      const double v = (i0 + lane < start) ? xs[i0 + lane] : nan;
+      const int m = start - i0 < 32 ? start - i0 : 32;
+      for (int j = 0; j < m; j++) {
+        const double vj = __shfl_sync(0xffffffffu, v, j);
+        if (!isnan(vj)) { ss = __dadd_rn(ss, __dmul_rn(vj, vj)); cnt++; }
+      }
     }
   }
   if (n <= start || cnt <= 1) {
-    for (long i = 0; i < n; i++) vs[i] = nan;
+    for (long i = lane; i < n; i += 32) vs[i] = nan;
     return;
   }
-  for (int i = 0; i < start; i++) vs[i] = nan;
+  for (int i = lane; i < start; i += 32) vs[i] = nan;
   double var = ss / (double)(cnt - 1);
-  vs[start] = sqrt(var);
+  if (lane == 0) vs[start] = sqrt(var);
   const double oml = 1.0 - lam;
-  for (long i = start + 1; i < n; i++) {
-    const double xp = xs[i - 1];
-    if (!isnan(xp)) var = __dadd_rn(__dmul_rn(lam, var), __dmul_rn(oml, __dmul_rn(xp, xp)));   // no FMA: numba does not fuse
-    vs[i] = sqrt(var);
+  // element i (start < i < n) needs x[i - 1]; blocks of 32 elements, the next block's observations prefetched
+  long base = start + 1;
+  double xp = (base + lane < n) ? xs[base + lane - 1] : nan;
+  for (; base < n; base += 32) {
+    const long nb = base + 32;
+    const double xnext = (nb + lane < n) ? xs[nb + lane - 1] : nan;
+    const unsigned miss = __ballot_sync(0xffffffffu, isnan(xp));
+    const double t = __dmul_rn(oml, __dmul_rn(xp, xp));
+    const int m = (int)(n - base < 32 ? n - base : 32);
+    double mine = 0.0;
+    if (m == 32) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) {
+        const double tj = __shfl_sync(0xffffffffu, t, j);
+        if (!((miss >> j) & 1u)) var = __dadd_rn(__dmul_rn(lam, var), tj);      // no FMA: numba does not fuse
+        if (lane == j) mine = var;
+      }
+    } else {
+      for (int j = 0; j < m; j++) {
+        const double tj = __shfl_sync(0xffffffffu, t, j);
+        if (!((miss >> j) & 1u)) var = __dadd_rn(__dmul_rn(lam, var), tj);
+        if (lane == j) mine = var;
+      }
+    }
+    if (lane < m) vs[base + lane] = sqrt(mine);
+    xp = xnext;
   }
 }
 
@@ -238,8 +336,8 @@ extern "C" {
 
 int pfml_xs_ols_daily(const double* X, const double* y, const long* day_ptr, int n_days, int K, double* coef, double* resid,
                       int* status, void* stream) {
-  if (!X || !y || !day_ptr || !coef || !resid || n_days <= 0 || K <= 0 || K > KC) {
-    set_error("pfml_xs_ols_daily: null/empty argument or K > %d", KC);
+  if (!X || !y || !day_ptr || !coef || !resid || n_days <= 0 || K <= 0 || K > KA - 1) {
+    set_error("pfml_xs_ols_daily: null/empty argument or K > %d", KA - 1);
     return -1;
   }
   cudaStream_t s = (cudaStream_t)stream;
@@ -270,7 +368,7 @@ int pfml_ewma_vol(const double* x, const long* series_ptr, int n_series, double 
   }
   cudaStream_t s = (cudaStream_t)stream;
   ProfScope ps(T_COV, s);
-  ewma_vol_kernel<<<ceil_div(n_series, 64), 64, 0, s>>>(n_series, x, series_ptr, lam, start, vol);
+  ewma_vol_kernel<<<ceil_div((long)n_series * 32, 128), 128, 0, s>>>(n_series, x, series_ptr, lam, start, vol);
   PFML_CHECK_LAUNCH();
   return 0;
 }
