@@ -708,10 +708,7 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     try:
-        run_ours(args, rank, world, local_rank)
-        if world > 1:
-            import torch.distributed as dist
-            dist.barrier()                      # rank 0 still times the CPU arm after the other ranks are done
+        run_ours(args, rank, world, local_rank)      # ranks != 0 leave once the collectives are done: rank 0 times the CPU arms alone
     finally:
         if world > 1:
             import torch.distributed as dist
