@@ -233,7 +233,7 @@ def hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, batch):
     # CPU arm on a bounded sample, extrapolated linearly (date-steps and refits are independent): numpy oracle, all BLAS threads
     import pfml_oracle as O
     use_all_host_threads()
-    small = make_bench_panel(syn, 3, 305)
+    small = make_bench_panel(syn, 10, 305)
     T, N, F = small.feats.shape
     rff_x = O.rff(small.feats.reshape(T * N, F), small.W).reshape(T, N, -1)
     vs = O.vol_scale_panel(small)
