@@ -47,15 +47,17 @@ __device__ __forceinline__ void slice16(const double (&x)[16], int e, int8_t* ds
   // int8 is g_t ^ 0x80 -- all ES balanced digits of an element come from one 64-bit add and one xor.
   constexpr unsigned long long Bz = 0x8080808080808080ull >> (8 * (8 - ES));
   unsigned lo[16], hi[16];
+  // F = round(x 2^(8 ES - 2 - e)): the scale is an exact power of two built in the exponent field, the product is exact and
+  // the hardware conversion rounds to nearest (ties to even).  A scale outside the normal range (a row / column whose
+  // largest element is below 2^-968, or a bogus exponent) gives all-zero digits; NaN / Inf have no digits either (they
+  // are flagged per matrix by the callers).
+  const int se = 1023 + (8 * ES - 2) - e;
+  const double sc = (se >= 1 && se <= 2046) ? __hiloint2double(se << 20, 0) : 0.0;
 #pragma unroll
   for (int k = 0; k < 16; k++) {
-    const long long bits = __double_as_longlong(x[k]);
-    const int ex = (int)((bits >> 52) & 0x7ff);
-    const unsigned long long mant = ((unsigned long long)bits & 0xFFFFFFFFFFFFFull) | (ex ? (1ull << 52) : 0ull);
-    const int sh = 1075 + e - (8 * ES - 2) - ex;           // |F| = round(mant 2^-sh)
-    // NaN / Inf (ex == 0x7ff) have no digits: they are flagged per matrix by the callers and sliced as zero (no shift >= 64)
-    const unsigned long long fv = (ex == 0 || ex == 0x7ff || sh >= 64 || sh <= -11) ? 0ull : (sh > 0 ? ((mant + (1ull << (sh - 1))) >> sh) : (mant << (-sh)));
-    const unsigned long long g = ((unsigned long long)(bits < 0 ? -(long long)fv : (long long)fv) + Bz) ^ Bz;
+    const double xs = x[k] * sc;
+    const long long fv = (fabs(xs) <= 9007199254740992.0 * 4.0) ? __double2ll_rn(xs) : 0ll;     // |F| <= 2^(8 ES - 2) for finite in-range values
+    const unsigned long long g = ((unsigned long long)fv + Bz) ^ Bz;
     lo[k] = (unsigned)g; hi[k] = (unsigned)(g >> 32);
   }
 #pragma unroll
