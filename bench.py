@@ -261,6 +261,48 @@ def hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, batch):
     return out
 
 
+def c5_universe(torch, dist, dev, lib, rank, world, dates=8):
+    """BASELINE configs[4] (stress universe): N = 3000 stocks (padded 3008), p = 1024 -- `dates` date-steps per rank, timed on
+    the device (max over ranks), with the INT8 result of one date checked against the FP64 DMMA path of the same library.
+    The oracle comparison at this universe size is a test (tests/test_baseline_configs_gpu.py, p = 64: one oracle date-step
+    takes a minute of CPU)."""
+    syn = importlib.import_module(PKG + ".synthetic")
+    dm = importlib.import_module(PKG + ".device")
+    panel = syn.make_panel(N=3000, T=syn.LB + 2 + dates, p=P_FEAT, seed=500 + rank, ragged=0.01)
+    months = [int(t) for t in panel.hot_months()]
+    dp = dm.DevicePanel(panel, dev)
+    sel, n_sel, n_max, NP = dm.universe(panel, months)
+    r = dm.DateStepRunner(dp, dates, n_max, want_signal=False)
+    r.set_batch(months, sel, n_sel)
+    r.run(); r.run()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); r.run(); r.run(); e1.record()
+    torch.cuda.synchronize(dev)
+    ms = torch.tensor([e0.elapsed_time(e1) / 2], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ok = int(r.status.abs().sum().item()) == 0
+    d1 = r.denom[0].clone()
+    lib.pfml_set_emulation(0)
+    r.run()
+    torch.cuda.synchronize(dev)
+    lib.pfml_set_emulation(1)
+    diff = float(((d1 - r.denom[0]).abs().max() / r.denom[0].abs().max()).item())
+    n_eff = int(n_sel.max())
+    P = P_FEAT + 1
+    flops = (23 + 22 + 4 / 3) * n_eff ** 3 + (24 + 4 + 2) * n_eff ** 2 * P + 2 * n_eff * P * P     # SURVEY 8(d) formulas at this n
+    out = {"workload": f"N=3000 (n = {n_eff}, padded {NP}), p={P_FEAT}, {dates} date-steps per GPU", "n_gpus": world,
+           "ms_per_date": float(ms.item()) / dates, "value": world * dates / (float(ms.item()) * 1e-3), "unit": UNIT,
+           "workspace_gb_per_gpu": r.ws_bytes / 1e9, "status_ok": ok, "int8_vs_dmma_denom_rel_diff": diff,
+           "algorithmic_tflops_per_gpu": flops * dates / (float(ms.item()) * 1e-3) * 1e-12}
+    del r, dp
+    torch.cuda.empty_cache()
+    return out
+
+
 def hbm_rows(torch, dev, lib):
     """The HBM-bound rows of the path (north_star item 5): achieved GB/s = algorithmic bytes / CUDA-event time.
     C2: 500 stocks x 5 040 trading days, K = 25 factors (a15 daily OLS, a16 factor covariance, a17 EWMA vol); a1: RFF of the
@@ -549,6 +591,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- hp-grid wall-time: the whole C3 + C4 pipeline at N GPUs (all ranks take part) ---------------------
     hp = hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, B) if not args.no_hp_grid else None
+    c5 = c5_universe(torch, dist, dev, lib, rank, world) if not args.no_hp_grid else None
     if comm is not None:
         comm.close()
     if rank != 0:
@@ -659,6 +702,7 @@ def run_ours(args, rank, world, local_rank):
                      "algorithmic_flops_per_date": off["total"],
                      "whole_step_algorithmic_tflops": off["total"] * B / (ms_total / args.steps * 1e-3) * 1e-12},
         "hp_grid": hp,
+        "c5_universe": c5,
         "hbm_rows": hb,
         "stages": stages,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",

@@ -5,7 +5,7 @@ print("value", d["value"], "ms/step", d["ms_per_step"], "e2e", d["e2e"]["value"]
       "diff", d["e2e"].get("max_abs_diff_vs_resident_path"), "six", d["value_six_digit_mode"]["value"])
 print(json.dumps(d["roofline"], indent=1)[:3500])
 print(json.dumps(d.get("hp_grid"), indent=1))
-print(json.dumps(d.get("hbm_rows"), indent=1))
+print(json.dumps(d.get("c5_universe"), indent=1)); print(json.dumps(d.get("hbm_rows"), indent=1))
 print(json.dumps(d["stages"], indent=1))
 print(d["details"])
 print(d["cpu_baseline"], d["clocks"], d["gpu_launches"])
