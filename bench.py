@@ -544,6 +544,32 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(ms6, op=dist.ReduceOp.MAX)
     value_six = world * B * args.steps / (float(ms6.item()) * 1e-3)
 
+    # ---- three bandwidths g of the same dates in one call (BASELINE configs[2] has 3 g; quirk Q10: m, the chains and the
+    # two inverses are shared over g): (date, g) pairs per second ------------------------------------------------------
+    rng3 = np.random.default_rng(9)
+    dp3 = device_mod.DevicePanel(panel, dev, extra_W=[np.sqrt(g_) * rng3.standard_normal(panel.W.shape) for g_ in np.exp([-2.0, -1.0])])
+    mg = device_mod.MultiGRunner(dp3, B, n_max)
+    mg.set_batch(months, sel, n_sel)
+    r3 = torch.zeros((3, nbk, Pn), dtype=torch.float64, device=dev)
+    d3 = torch.zeros((3, nbk, Pn, Pn), dtype=torch.float64, device=dev)
+    mg.run(bucket, nbk, r3, d3)
+    barrier()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    for _ in range(args.steps):
+        mg.run(bucket, nbk, r3, d3)
+    g1.record()
+    barrier()
+    ms3 = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms3, op=dist.ReduceOp.MAX)
+    value_3g = world * 3 * B * args.steps / (float(ms3.item()) * 1e-3)
+    ms_3g = float(ms3.item()) / args.steps
+    assert int(mg.status.abs().sum().item()) == 0
+    same_g0 = bool(torch.equal(mg.denom[0], runner.denom))
+    del mg, dp3, r3, d3
+    torch.cuda.empty_cache()
+
     # ---- live per-kernel accounting (CUDA events around every launch group, same steps) ------------
     nt = lib.pfml_prof_ntags()
     pms, pfl, pln = (np.zeros(nt) for _ in range(3))
@@ -666,6 +692,12 @@ def run_ours(args, rank, world, local_rank):
         "value_six_digit_mode": {"value": value_six, "unit": UNIT,
                                  "note": "pfml_set_emulation(2): 6 of 7 digits for the non-compounding products; 7e-12 of the "
                                          "DMMA result instead of 1e-13 (tolerance 1e-8); not the default"},
+        "value_three_g_shared": {"value": value_3g, "unit": "(date, g) steps/s", "ms_per_step": ms_3g, "g_per_date": 3,
+                                 "g0_bit_identical_to_single_g_step": same_g0,
+                                 "note": "pfml_date_steps_multi_g: the 3 bandwidths of BASELINE configs[2] for the same 148 dates in one call; "
+                                         "Sigma, m_func, the gtm chains and the two inverses do not depend on g (the reference recomputes "
+                                         "them per g, PFML_Input_Data.py:225,318) and are computed once; every g's outputs are bit-identical "
+                                         "to the single-g step; this is what hp_grid runs"},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_packed,
                 "entry_point": "pfml_date_steps_host_packed",
                 "outputs": "r_tilde, signal_t and the upper triangles of risk and tc (denom = risk + tc exactly; all three symmetric): "

@@ -97,6 +97,20 @@ int pfml_date_steps_bucketed(const pfml_panel_t* panel, int B, int n_max, const 
                              double* risk, double* tc, double* signal_t, int* status, void* workspace, size_t workspace_bytes,
                              void* stream);
 
+/* a3..a9 (+ a11) for G bandwidths g of the SAME dates in one call (PFML_Input_Data.py:225 loops g outside the date loop
+ * and recomputes everything per g; quirk Q10: Sigma, Lambda, m_func, the gtm chains and the two `const` matrices of
+ * :400-456 do not depend on g).  rff_g is a HOST array of G device panels [T*N][p] (one W per g; panel->rff is ignored),
+ * the output arguments are HOST arrays of G device pointers (risk_g / tc_g / signal_t_g and their entries may be NULL;
+ * bucket NULL = no window sums).  m, the chain, the sums of the chain and the two inverses are computed once; per g only
+ * a6, the n x P sums, the two solve products and a9 run.  Every g's outputs are bit-identical to a single-g
+ * pfml_date_steps call on that g's panel.  Shapes the shared path does not cover (FP64 DMMA mode, universes beyond the
+ * INT8 depth limit) fall back to one full pass per g.  status [B] ORs the flags of all g.  Workspace as pfml_date_steps. */
+int pfml_date_steps_multi_g(const pfml_panel_t* panel, int G, const double* const* rff_g, int B, int n_max, const int* date_t,
+                            const int* sel, const int* n_sel, const int* bucket, int n_buckets, double* const* r_sum_g,
+                            double* const* d_sum_g, double* const* r_tilde_g, double* const* denom_g, double* const* risk_g,
+                            double* const* tc_g, double* const* signal_t_g, int* status, void* workspace, size_t workspace_bytes,
+                            void* stream);
+
 /* Stage-level entry points: the same kernels as pfml_date_steps, stopped / started at a stage boundary, so that
  * each stage can be called, parity-tested and profiled on its own.  All take the workspace of
  * pfml_date_steps_workspace_bytes and the same date_t / sel / n_sel arrays; matrices are [B][NP][.] with rows

@@ -60,6 +60,9 @@ SIGNATURES = {
                                            C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_size_t, C.c_void_p]),
+    "pfml_date_steps_multi_g": (C.c_int, [C.POINTER(PanelStruct), C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "pfml_standardize_scale": (C.c_int, [C.POINTER(PanelStruct), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "pfml_omega_batched": (C.c_int, [C.POINTER(PanelStruct), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,

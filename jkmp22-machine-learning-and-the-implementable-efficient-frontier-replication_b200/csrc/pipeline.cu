@@ -341,6 +341,13 @@ struct StepOpts {
   double *omega_out = nullptr, *omega_chg_out = nullptr, *m_out = nullptr;    // un-tilded, [B][NP][P] / [B][NP][NP]
   const double *omega_in = nullptr, *omega_chg_in = nullptr;                  // a9 from a given omega / omega_chg [B][NP][P]
   bool stop_after_omega = false;
+  bool keep_status = false;                 // do not clear `status` first (a further pass over the same dates)
+  // further bandwidths g = 1 .. n_extra of the SAME dates (quirk Q10: m, the chain and the two inverses do not depend on
+  // g): their feature panels and outputs (entries of risk / tc / signal / sums may be null)
+  int n_extra = 0;
+  const double* const* x_rff = nullptr;
+  double* const* x_r_tilde = nullptr; double* const* x_denom = nullptr; double* const* x_risk = nullptr; double* const* x_tc = nullptr;
+  double* const* x_signal = nullptr; double* const* x_r_sum = nullptr; double* const* x_d_sum = nullptr;
 };
 
 static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const int* date_t, const int* sel, const int* n_sel,
@@ -369,7 +376,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
   if (!risk) risk = w.risk_tmp;
   if (!tc) tc = w.tc_tmp;
   const long NN = (long)NP * NP, ldP = w.ldP, nP = (long)NP * ldP, sStack = (long)(NP + KP) * ldP;
-  if (status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
+  if (status && !opt.keep_status) PFML_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
 
   // ---- a3/a4 gathers ------------------------------------------------------------------------------
   {
@@ -410,6 +417,10 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     if (E) { g.E = E; g.lde = ldP; g.sE = sE; g.beta = 1.0; }
     return gemm(g, B, s);
   };
+  double* mt = nullptr;
+  const double* bk[16] = {};
+  double* B11 = w.m.x;
+  const size_t slabS = emu_b_slices_bytes(B, NP, P);
   if (opt.omega_in) {
     // ---- stage entry: a9 from a given omega / omega_chg (un-tilded): omega~ = Lambda^1/2 omega ----------
     if (!opt.omega_chg_in) { set_error("pfml_rtilde_denom_batched: omega_chg missing"); return -1; }
@@ -417,7 +428,6 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     PFML_TRY(tilde_rows(B, NP, P, opt.omega_chg_in, n_sel, w.v.sl, w.OMC, ldP, nP, s));
   } else {
   // ---- a5 m_tilde: m~_0 by quadrature + Woodbury (stieltjes.cu), then the fixed-point inverses -----
-  double* mt = nullptr;
   {
     ProfScope ps(T_MFUNC, s);
     PFML_TRY(build_x_factor(pv, B, NP, date_t, sel, n_sel, w.v, w.m.x, w.m.sgr, w.m.yv, s));
@@ -434,17 +444,15 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     if (direct) PFML_TRY(emu_standardize_slices(pv, B, NP, P, 2, lb, date_t, sel, n_sel, w.v, w.eSs, w.eSsb, w.eerr, s));
   }
   // free n x n buffers after m_tilde: x, sgr, Mdb, Ya, Yb, Wk, T1 and whichever of {mt, Xinv} is not `mt`
-  double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr; double* B11 = w.m.x;
+  double* Bt_a = w.m.Ya; double* Bt_b = w.m.Yb; double* CB = w.m.Mdb; double* CBs = w.m.sgr;
   double* spare = (mt == w.m.mt) ? w.m.Xinv : w.m.mt;
 
   double* Z = nullptr;
-  const size_t slabS = emu_b_slices_bytes(B, NP, P);
   if (direct) {
     // ---- a7 + a8 together: for k = 1 .. lb-1 the slices of B~_k serve two products, the chain step
     //   B~_{k+1} = B~_k m~ G_{k+1} and the term Z += B~_k S~_{k+1} (Z starts as S~_1).  m~ is sliced once as a B operand.
     PFML_TRY(chain_init(B, NP, mt, gv(1), sg, Bt_a, CB, s));
     PFML_TRY(emu_slice_b(mt, NP, NN, NP, NP, B, w.eMs, w.esm, w.eex, w.eerr, s));
-    const double* bk[16];
     bk[0] = Bt_a;
     Z = w.Za;
     for (int k = 1; k < lb; k++) {
@@ -597,8 +605,8 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     return 0;
   }
 
-  // ---- a9 r_tilde, risk, tc, denom ----------------------------------------------------------------
-  {
+  // ---- a9 r_tilde, risk, tc, denom (from omega~ in w.OM, omega~_chg in w.OMC) ------------------------------
+  auto a9_stage = [&](double* r_tilde, double* denom, double* risk, double* tc, double* r_sum, double* d_sum) -> int {
     ProfScope ps(T_DENOM, s);
     bool fused_sums = false;
     PFML_TRY(gemv_t(B, NP, P, w.OM, ldP, sStack, w.v.rv, NP, r_tilde, P, s));
@@ -641,7 +649,7 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
       xt.sym = true; xt.az = w.v.scal + 0; xt.s_az = NSCAL; xt.digits = xq.digits;
       PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, P, P, NP, B, 1.0, nullptr, 0, 0.0, nullptr, 0, 0, tc, P, (long)P * P, xt, w.eerr, s));
       // denom = risk + tc; lower triangles = copies of the upper; the per-window sums of denom ride along
-      PFML_TRY(sym_finish(B, P, risk, tc, denom, w.ezf, bad, opt.bucket, opt.n_buckets, opt.d_sum, s));
+      PFML_TRY(sym_finish(B, P, risk, tc, denom, w.ezf, bad, opt.bucket, opt.n_buckets, d_sum, s));
       PFML_TRY(poison_bad_dates(B, P, bad, r_tilde, nullptr, nullptr, nullptr, s));
       fused_sums = true;
     } else {
@@ -668,9 +676,59 @@ static int date_steps_impl(const pfml_panel_t* panel, int B, int n_max, const in
     }
     // ---- a11 expanding-window sums (PFML_Search_Coef.py:77-88, :112-121) of this batch, accumulated into r_sum / d_sum ----
     if (opt.bucket && opt.n_buckets > 0) {
-      if (opt.r_sum) PFML_TRY(bucket_accumulate(B, P, r_tilde, opt.bucket, opt.n_buckets, opt.r_sum, s));
-      if (opt.d_sum && !fused_sums) PFML_TRY(bucket_accumulate(B, (long)P * P, denom, opt.bucket, opt.n_buckets, opt.d_sum, s));
+      if (r_sum) PFML_TRY(bucket_accumulate(B, P, r_tilde, opt.bucket, opt.n_buckets, r_sum, s));
+      if (d_sum && !fused_sums) PFML_TRY(bucket_accumulate(B, (long)P * P, denom, opt.bucket, opt.n_buckets, d_sum, s));
     }
+    return 0;
+  };
+  PFML_TRY(a9_stage(r_tilde, denom, risk, tc, opt.r_sum, opt.d_sum));
+
+  // ---- further bandwidths of the same dates (quirk Q10): only the g-dependent stages are repeated ----------------
+  // a6 on that g's feature panel, the n x P sums (the A digits of every kept B~_k are cut again: 11 small launches), the two
+  // solve products against the shared inverses, a9.  Same kernels on the same operands as a single-g call with that
+  // panel, in a different launch order: the results are bit-identical to it.
+  for (int g = 0; g < opt.n_extra; g++) {
+    if (!direct || opt.omega_in) { set_error("pfml_date_steps_multi_g: shared path unavailable for this shape"); return -2; }
+    if (emu) PFML_CUDA_OK(cudaMemsetAsync(bad, 0, sizeof(int) * B, s));      // the flags of the previous g are in `status` already
+    PanelView pg = pv;
+    pg.rff = opt.x_rff[g];
+    double* sig_g = opt.x_signal ? opt.x_signal[g] : nullptr;
+    double* risk_g = (opt.x_risk && opt.x_risk[g]) ? opt.x_risk[g] : w.risk_tmp;
+    double* tc_g = (opt.x_tc && opt.x_tc[g]) ? opt.x_tc[g] : w.tc_tmp;
+    {
+      ProfScope ps(T_STD, s);
+      PFML_TRY(standardize(pg, B, NP, P, ldP, date_t, sel, n_sel, w.v, w.St, sig_g, false, 2, s));
+      PFML_TRY(emu_standardize_slices(pg, B, NP, P, 2, lb, date_t, sel, n_sel, w.v, w.eSs, w.eSsb, w.eerr, s));
+    }
+    double* Zg = w.Za;
+    {
+      ProfScope ps(T_HORNER, s);
+      for (int k = 1; k < lb; k++) {
+        PFML_TRY(emu_slice_a(bk[k - 1], NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+        const double* E = (k == 1) ? St(1) : Zg;
+        PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eSs + (size_t)(k - 1) * slabS, w.eSsb + (size_t)(k - 1) * B * P, NP, P, NP, B, 1.0, nullptr,
+                            0, 1.0, E, ldP, (k == 1) ? sSt : nP, Zg, ldP, nP, xq, w.eerr, s));
+      }
+      PFML_TRY(emu_slice_a(mt, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+      if (NP <= 1024) {
+        PFML_TRY(emu_slice_nmajor512(Zg, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, nullptr, nullptr, w.eerr, s, gv(0), sg));
+      } else {
+        PFML_TRY(row_scale(B, NP, P, ldP, nP, Zg, gv(0), sg, w.Zb, ldP, nP, s));
+        PFML_TRY(emu_slice_b(w.Zb, ldP, nP, NP, P, B, w.eBs, w.esb, w.eex, w.eerr, s));
+      }
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eBs, w.esb, NP, P, NP, B, 1.0, nullptr, 0, 1.0, St(0), ldP, sSt, w.Nn, ldP, nP, xq, w.eerr, s));
+      PFML_TRY(emu_slice_a(B11, NP, NN, NP, NP, B, w.eAs, w.esa, w.eerr, s));
+      PFML_TRY(emu_mma_ex(w.eAs, w.esa, w.eSs + (size_t)(lb - 1) * slabS, w.eSsb + (size_t)(lb - 1) * B * P, NP, P, NP, B, 1.0, nullptr, 0,
+                          1.0, Zg, ldP, nP, w.Nl1, ldP, nP, xq, w.eerr, s));
+    }
+    {
+      ProfScope ps(T_SOLVE, s);
+      emu_a_cur = nullptr;
+      PFML_TRY(nxP(w.XC, w.Nn, nP, 1.0, nullptr, 0, nullptr, 0, w.OM, sStack));
+      PFML_TRY(nxP(w.XCl1, w.Nl1, nP, -1.0, w.v.g0raw, NP, w.OM, sStack, w.OMC, nP));
+    }
+    PFML_TRY(a9_stage(opt.x_r_tilde[g], opt.x_denom[g], risk_g, tc_g, opt.x_r_sum ? opt.x_r_sum[g] : nullptr,
+                      opt.x_d_sum ? opt.x_d_sum[g] : nullptr));
   }
   return 0;
 }
@@ -774,6 +832,51 @@ int pfml_date_steps_bucketed(const pfml_panel_t* panel, int B, int n_max, const 
   o.bucket = bucket; o.n_buckets = n_buckets; o.r_sum = r_sum; o.d_sum = d_sum;
   return date_steps_impl(panel, B, n_max, date_t, sel, n_sel, r_tilde, denom, risk, tc, signal_t, status, workspace, workspace_bytes,
                          (cudaStream_t)stream, o);
+}
+
+int pfml_date_steps_multi_g(const pfml_panel_t* panel, int G, const double* const* rff_g, int B, int n_max, const int* date_t,
+                            const int* sel, const int* n_sel, const int* bucket, int n_buckets, double* const* r_sum_g,
+                            double* const* d_sum_g, double* const* r_tilde_g, double* const* denom_g, double* const* risk_g,
+                            double* const* tc_g, double* const* signal_t_g, int* status, void* workspace, size_t workspace_bytes,
+                            void* stream) {
+  if (!panel || G < 1 || G > 16 || !rff_g || !r_tilde_g || !denom_g) {
+    set_error("pfml_date_steps_multi_g: null argument or G outside 1..16");
+    return -1;
+  }
+  for (int g = 0; g < G; g++)
+    if (!rff_g[g] || !r_tilde_g[g] || !denom_g[g]) { set_error("pfml_date_steps_multi_g: null panel / output for g = %d", g); return -1; }
+  if (bucket && (n_buckets <= 0 || !r_sum_g || !d_sum_g)) { set_error("pfml_date_steps_multi_g: window sums requested without buffers"); return -1; }
+  pfml_panel_t p0 = *panel;
+  p0.rff = rff_g[0];
+  const int NP = pfml_padded_n(n_max), P = panel->p + 1;
+  // the shared path needs the INT8 direct form (padded universe a multiple of 64 up to the emulation's depth limit, lb <= 17)
+  const bool shared = G > 1 && emu_mode() != 0 && emu_shape_ok(NP, P, NP) && emu_shape_ok(NP, NP, NP) && panel->lb - 1 <= 16 && panel->lb + 2 >= 5;
+  StepOpts o;
+  o.bucket = bucket; o.n_buckets = bucket ? n_buckets : 0;
+  o.r_sum = bucket ? r_sum_g[0] : nullptr; o.d_sum = bucket ? d_sum_g[0] : nullptr;
+  if (shared) {
+    o.n_extra = G - 1;
+    o.x_rff = rff_g + 1; o.x_r_tilde = r_tilde_g + 1; o.x_denom = denom_g + 1;
+    o.x_risk = risk_g ? risk_g + 1 : nullptr; o.x_tc = tc_g ? tc_g + 1 : nullptr; o.x_signal = signal_t_g ? signal_t_g + 1 : nullptr;
+    o.x_r_sum = bucket ? r_sum_g + 1 : nullptr; o.x_d_sum = bucket ? d_sum_g + 1 : nullptr;
+  }
+  PFML_TRY(date_steps_impl(&p0, B, n_max, date_t, sel, n_sel, r_tilde_g[0], denom_g[0], risk_g ? risk_g[0] : nullptr, tc_g ? tc_g[0] : nullptr,
+                           signal_t_g ? signal_t_g[0] : nullptr, status, workspace, workspace_bytes, (cudaStream_t)stream, o));
+  if (!shared) {
+    // no sharing possible for this shape / mode: one full pass per further bandwidth (status flags accumulate by OR)
+    for (int g = 1; g < G; g++) {
+      pfml_panel_t pg = *panel;
+      pg.rff = rff_g[g];
+      StepOpts og;
+      og.bucket = bucket; og.n_buckets = bucket ? n_buckets : 0;
+      og.r_sum = bucket ? r_sum_g[g] : nullptr; og.d_sum = bucket ? d_sum_g[g] : nullptr;
+      og.keep_status = true;
+      PFML_TRY(date_steps_impl(&pg, B, n_max, date_t, sel, n_sel, r_tilde_g[g], denom_g[g], risk_g ? risk_g[g] : nullptr,
+                               tc_g ? tc_g[g] : nullptr, signal_t_g ? signal_t_g[g] : nullptr, status, workspace, workspace_bytes,
+                               (cudaStream_t)stream, og));
+    }
+  }
+  return 0;
 }
 
 // ---- stage-level entry points: a6, a3..a8, a9 on their own -----------------------------------------

@@ -32,7 +32,9 @@ class DevicePanel:
     Layout: dense [T*N] rows (month-major), FP64, row-major; see pfml_panel_t in include/pfml_b200.h.
     """
 
-    def __init__(self, panel, device="cuda:0"):
+    def __init__(self, panel, device="cuda:0", extra_W=()):
+        """``extra_W``: further random-feature matrices (one per additional bandwidth g, quirk Q10); their feature panels
+        are kept in ``self.rffs`` (``self.rffs[0]`` is the panel of ``panel.W``)."""
         lib = _lib.load()
         self.device = torch.device(device)
         self.host = panel
@@ -46,6 +48,12 @@ class DevicePanel:
             self.W = W
             self.rff = torch.empty((T * N, self.p), dtype=torch.float64, device=self.device)
             check(lib.pfml_rff_sincos(_ptr(feats), _ptr(W), T * N, F, self.p // 2, _ptr(self.rff), s), "pfml_rff_sincos")
+            self.rffs = [self.rff]
+            for Wx in extra_W:
+                Wd = _dev(Wx, self.device)
+                r = torch.empty((T * N, self.p), dtype=torch.float64, device=self.device)
+                check(lib.pfml_rff_sincos(_ptr(feats), _ptr(Wd), T * N, F, self.p // 2, _ptr(r), s), "pfml_rff_sincos")
+                self.rffs.append(r)
             self.fct_load = _dev(panel.fct_load.reshape(T * N, K), self.device)
             self.fct_cov = _dev(panel.fct_cov, self.device)
             self.ivol = _dev(panel.ivol.reshape(-1), self.device)
@@ -83,6 +91,55 @@ def universe(panel, months):
     for b, s in enumerate(sels):
         sel[b, :len(s)] = s
     return sel, n_sel, n_max, NP
+
+
+class MultiGRunner:
+    """B date-steps for the G bandwidths of a DevicePanel built with ``extra_W`` in one call (pfml_date_steps_multi_g):
+    m, the chains and the two inverses are shared over g.  Outputs per g: r_tilde [G, B, P], denom [G, B, P, P] (risk / tc
+    / signal_t optional); ``run(bucket, nb, r_sum, d_sum)`` also accumulates the per-window sums r_sum [G, nb, P],
+    d_sum [G, nb, P, P]."""
+
+    def __init__(self, dpanel, B, n_max, want_risk_tc=False, want_signal=False):
+        lib = _lib.load()
+        self.dp, self.B, self.n_max = dpanel, B, n_max
+        self.G = len(dpanel.rffs)
+        self.NP = lib.pfml_padded_n(n_max)
+        P = self.P = dpanel.p + 1
+        dev = dpanel.device
+        f64 = dict(dtype=torch.float64, device=dev)
+        G = self.G
+        self.r_tilde = torch.empty((G, B, P), **f64)
+        self.denom = torch.empty((G, B, P, P), **f64)
+        self.risk = torch.empty((G, B, P, P), **f64) if want_risk_tc else None
+        self.tc = torch.empty((G, B, P, P), **f64) if want_risk_tc else None
+        self.signal_t = torch.empty((G, B, self.NP, P), **f64) if want_signal else None
+        self.status = torch.zeros(B, dtype=torch.int32, device=dev)
+        self.ws_bytes = lib.pfml_date_steps_workspace_bytes(C.byref(dpanel.struct), B, n_max)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
+        self.date_t = torch.empty(B, dtype=torch.int32, device=dev)
+        self.sel = torch.empty((B, self.NP), dtype=torch.int32, device=dev)
+        self.n_sel = torch.empty(B, dtype=torch.int32, device=dev)
+
+    set_batch = None      # bound below (same as DateStepRunner.set_batch)
+
+    @staticmethod
+    def _ptrs(t, G):
+        arr = (C.c_void_p * G)()
+        for g in range(G):
+            arr[g] = t[g].data_ptr() if t is not None else None
+        return arr
+
+    def run(self, bucket=None, n_buckets=0, r_sum=None, d_sum=None):
+        lib = _lib.load()
+        G = self.G
+        rff = self._ptrs(self.dp.rffs, G)
+        opt = lambda t: self._ptrs(t, G) if t is not None else None
+        with torch.cuda.device(self.dp.device):
+            check(lib.pfml_date_steps_multi_g(C.byref(self.dp.struct), G, rff, self.b, self.n_max, _ptr(self.date_t), _ptr(self.sel),
+                                              _ptr(self.n_sel), _ptr(bucket) if bucket is not None else None, int(n_buckets),
+                                              opt(r_sum), opt(d_sum), self._ptrs(self.r_tilde, G), self._ptrs(self.denom, G),
+                                              opt(self.risk), opt(self.tc), opt(self.signal_t), _ptr(self.status), _ptr(self.ws),
+                                              self.ws_bytes, _stream_ptr()), "pfml_date_steps_multi_g")
 
 
 class DateStepRunner:
@@ -136,6 +193,9 @@ class DateStepRunner:
                                                _ptr(self.r_tilde), _ptr(self.denom), _ptr(self.risk), _ptr(self.tc),
                                                _ptr(self.signal_t), _ptr(self.status), _ptr(self.ws), self.ws_bytes, _stream_ptr()),
                   "pfml_date_steps_bucketed")
+
+
+MultiGRunner.set_batch = DateStepRunner.set_batch
 
 
 def date_steps(panel, months, device="cuda:0", dpanel=None):

@@ -2,8 +2,9 @@
 
 For every bandwidth g (PFML_Input_Data.py:225; one W per g, quirk Q1):
 
-  1. this rank's contiguous block of dates (sharding.shard_dates) runs through ``pfml_date_steps_bucketed`` in batches:
-     r_tilde / denom of every date (PFML_Input_Data.py:318-491) and, fused into the a9 finish kernel, the per-window
+  1. this rank's contiguous block of dates (sharding.shard_dates) runs through ``pfml_date_steps_multi_g`` in batches:
+     r_tilde / denom of every date and every g (PFML_Input_Data.py:318-491; Sigma, m_func, the gtm chains and the two
+     ``const`` inverses of a date are shared over g, quirk Q10) and, fused into the a9 finish kernel, the per-window
      partial sums of PFML_Search_Coef.py:77-88, :112-121 over this rank's dates;
   2. one FP64 NCCL all-reduce of the ``[windows] x (P + P^2 + 1)`` partial sums (``pfml_comm_allreduce_sums``) -- the one
      real exchange of the path;
@@ -42,32 +43,33 @@ def slice_panel(panel, t0, t1, W=None):
     return type(panel)(**kw)
 
 
-def partial_sums(panel, W, months, mine, hp_sorted, dev, batch=148):
-    """Per-window partial sums of one rank: date-steps of ``mine`` (a sub-list of ``months``) with the sums fused in.
-    Returns r_sum [nb, P], d_sum [nb, P, P], cnt [nb] on ``dev``."""
-    nb = len(hp_sorted) + 1
-    P = 2 * W.shape[1] + 1
-    r_sum = torch.zeros((nb, P), dtype=torch.float64, device=dev)
-    d_sum = torch.zeros((nb, P, P), dtype=torch.float64, device=dev)
+def partial_sums(panel, W_by_g, months, mine, hp_sorted, dev, batch=148):
+    """Per-window partial sums of one rank for every bandwidth g: date-steps of ``mine`` (a sub-list of ``months``) with
+    the sums fused in; m, the chains and the two inverses of a date are computed once and shared over g
+    (pfml_date_steps_multi_g, quirk Q10).  Returns r_sum [G, nb, P], d_sum [G, nb, P, P], cnt [nb] on ``dev``."""
+    nb, G = len(hp_sorted) + 1, len(W_by_g)
+    P = 2 * W_by_g[0].shape[1] + 1
+    r_sum = torch.zeros((G, nb, P), dtype=torch.float64, device=dev)
+    d_sum = torch.zeros((G, nb, P, P), dtype=torch.float64, device=dev)
     cnt = torch.zeros(nb, dtype=torch.float64, device=dev)
     if len(mine) == 0:
         return r_sum, d_sum, cnt
     t0, t1 = sharding.panel_slice_for(mine, panel.lb)
-    sub = slice_panel(panel, t0, t1, W=W)
-    dp = dm.DevicePanel(sub, dev)
+    sub = slice_panel(panel, t0, t1, W=W_by_g[0])
+    dp = dm.DevicePanel(sub, dev, extra_W=W_by_g[1:])
     local = np.asarray(mine) - t0
     bucket_all = sc.rank_buckets(panel.month_ends[np.asarray(mine)], hp_sorted)
     cnt += torch.as_tensor(np.bincount(bucket_all[bucket_all >= 0], minlength=nb).astype(np.float64)).to(dev)
     sel, n_sel, n_max, NP = dm.universe(sub, local)
     bsz = min(batch, len(local))
-    runner = dm.DateStepRunner(dp, bsz, n_max, want_risk_tc=False, want_signal=False)
+    runner = dm.MultiGRunner(dp, bsz, n_max)
     for b0 in range(0, len(local), bsz):
         sl = slice(b0, min(b0 + bsz, len(local)))
         runner.set_batch(local[sl], sel[sl], n_sel[sl])
         bk = torch.as_tensor(bucket_all[sl].astype(np.int32)).to(dev)
-        runner.run_bucketed(bk, nb, r_sum, d_sum)
-    if int(runner.status.abs().sum()) != 0:
-        raise RuntimeError("numerical failure flag set in the date-steps")
+        runner.run(bk, nb, r_sum, d_sum)
+        if int(runner.status.abs().sum()) != 0:
+            raise RuntimeError("numerical failure flag set in the date-steps")
     return r_sum, d_sum, cnt
 
 
@@ -84,17 +86,20 @@ def hp_grid_pipeline(panel, W_by_g, months, hp_years, p_vec, l_vec, comm=None, d
     rank, world = (comm.rank, comm.world) if comm is not None else (0, 1)
     out = {}
     tm = dict(date_steps_s=0.0, exchange_s=0.0, ridge_s=0.0, allreduce_bytes=0)
-    for g_index, W in enumerate(W_by_g):
-        torch.cuda.synchronize(dev)
-        ta = time.perf_counter()
-        if virtual_world:
-            parts = [partial_sums(panel, W, months, sharding.shard_dates(months, r, virtual_world), hp_sorted, dev, batch)
-                     for r in range(virtual_world)]
-            r_sum, d_sum, cnt = parts[0]
-            for pr, pd_, pc in parts[1:]:                              # what the all-reduce computes, in rank order
-                r_sum += pr; d_sum += pd_; cnt += pc
-        else:
-            r_sum, d_sum, cnt = partial_sums(panel, W, months, sharding.shard_dates(months, rank, world), hp_sorted, dev, batch)
+    torch.cuda.synchronize(dev)
+    ta = time.perf_counter()
+    if virtual_world:
+        parts = [partial_sums(panel, W_by_g, months, sharding.shard_dates(months, r, virtual_world), hp_sorted, dev, batch)
+                 for r in range(virtual_world)]
+        r_all, d_all, cnt_all = parts[0]
+        for pr, pd_, pc in parts[1:]:                              # what the all-reduce computes, in rank order
+            r_all += pr; d_all += pd_; cnt_all += pc
+    else:
+        r_all, d_all, cnt_all = partial_sums(panel, W_by_g, months, sharding.shard_dates(months, rank, world), hp_sorted, dev, batch)
+    torch.cuda.synchronize(dev)
+    tm["date_steps_s"] = time.perf_counter() - ta
+    for g_index in range(len(W_by_g)):
+        r_sum, d_sum, cnt = r_all[g_index], d_all[g_index], cnt_all.clone()
         torch.cuda.synchronize(dev)
         tb = time.perf_counter()
         if comm is not None:
@@ -121,7 +126,6 @@ def hp_grid_pipeline(panel, W_by_g, months, hp_years, p_vec, l_vec, comm=None, d
         torch.cuda.synchronize(dev)
         td = time.perf_counter()
         out[g_index] = {year: {int(p): betas[int(p)][k].cpu().numpy() for p in p_vec} for k, year in enumerate(hp_sorted)}
-        tm["date_steps_s"] += tb - ta
         tm["exchange_s"] += tc - tb
         tm["ridge_s"] += td - tc
     if timing is not None:

@@ -125,3 +125,47 @@ def _bucketed_case(dev, syn, sc, torch, n, p):
     assert torch.equal(r_sum, r_ref + 1.5)
     assert torch.equal(d_sum, d_ref - 0.25)
     assert int(run.status.abs().sum()) == 0
+
+
+def test_multi_g_shares_m_and_chain_bit_identical(dev, syn):
+    """pfml_date_steps_multi_g: three bandwidths of the same dates with m, the chains and the inverses computed once
+    (quirk Q10).  Every g's outputs and window sums equal the single-g call on that g's panel BIT FOR BIT, in the INT8
+    direct form (n = 500) and on the per-g fallback (FP64 DMMA mode)."""
+    import dataclasses
+    import torch
+    lib = pkg("_lib").load()
+    panel = syn.make_panel(N=500, T=18, p=32, seed=65, ragged=0.02)
+    rng = np.random.default_rng(66)
+    Ws = [panel.W, 0.3 * rng.standard_normal(panel.W.shape), 0.6 * rng.standard_normal(panel.W.shape)]
+    months = [13, 14, 15, 16]
+    sel, n_sel, n_max, NP = dev.universe(panel, months)
+    bucket = torch.as_tensor(np.array([0, 1, 1, 0], dtype=np.int32)).cuda()
+    P = panel.p + 1
+    for mode in (1, 0):
+        lib.pfml_set_emulation(mode)
+        try:
+            dp = dev.DevicePanel(panel, extra_W=Ws[1:])
+            mg = dev.MultiGRunner(dp, len(months), n_max, want_risk_tc=True, want_signal=True)
+            mg.set_batch(months, sel, n_sel)
+            r_sum = torch.zeros((3, 2, P), dtype=torch.float64, device="cuda")
+            d_sum = torch.zeros((3, 2, P, P), dtype=torch.float64, device="cuda")
+            mg.run(bucket, 2, r_sum, d_sum)
+            torch.cuda.synchronize()
+            assert int(mg.status.abs().sum()) == 0
+            for g, W in enumerate(Ws):
+                one = dev.DateStepRunner(dev.DevicePanel(dataclasses.replace(panel, W=W)), len(months), n_max)
+                one.set_batch(months, sel, n_sel)
+                rs, ds = torch.zeros((2, P), dtype=torch.float64, device="cuda"), torch.zeros((2, P, P), dtype=torch.float64, device="cuda")
+                one.run_bucketed(bucket, 2, rs, ds)
+                torch.cuda.synchronize()
+                for name in ("r_tilde", "denom", "risk", "tc", "signal_t"):
+                    assert torch.equal(getattr(mg, name)[g], getattr(one, name)), (mode, g, name)
+                assert torch.equal(r_sum[g], rs) and torch.equal(d_sum[g], ds), (mode, g)
+        finally:
+            lib.pfml_set_emulation(1)
+    # and one g against the oracle
+    pg = dataclasses.replace(panel, W=Ws[2])
+    rff_x, vs = _pre(pg)
+    o = O.date_step(pg, 14, rff_x, vs)
+    for name in ("r_tilde", "denom", "risk", "tc"):
+        assert relerr(getattr(mg, name)[2, 1].cpu().numpy(), o[name]) < TOL, name
