@@ -566,7 +566,9 @@ def run_ours(args, rank, world, local_rank):
     value_3g = world * 3 * B * args.steps / (float(ms3.item()) * 1e-3)
     ms_3g = float(ms3.item()) / args.steps
     assert int(mg.status.abs().sum().item()) == 0
-    same_g0 = bool(torch.equal(mg.denom[0], runner.denom))
+    step()                                                 # the single-g step in the default mode again (the last one ran in mode 2)
+    torch.cuda.synchronize(dev)
+    same_g0 = bool(torch.equal(mg.denom[0], runner.denom)) and bool(torch.equal(mg.r_tilde[0], runner.r_tilde))
     del mg, dp3, r3, d3
     torch.cuda.empty_cache()
 
