@@ -785,8 +785,21 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    # Ranks != 0 are done once the collectives are: rank 0 then times the CPU arms alone.  They must not spin meanwhile (a
+    # NCCL barrier or the process-group shutdown busy-waits on a host core each, and an over-subscribed OpenBLAS collapses),
+    # so they sleep on a flag file until rank 0 is through, and everybody tears the process group down together.
+    flag = os.path.join("/tmp", "pfml_bench_done_%s_%s" % (os.environ.get("MASTER_PORT", "0"), os.environ.get("TORCHELASTIC_RUN_ID", "x")))
+    if world > 1 and rank == 0 and os.path.exists(flag):
+        os.remove(flag)
     try:
-        run_ours(args, rank, world, local_rank)      # ranks != 0 leave once the collectives are done: rank 0 times the CPU arms alone
+        run_ours(args, rank, world, local_rank)
+        if world > 1:
+            if rank == 0:
+                open(flag, "w").close()
+            else:
+                t_wait = time.time()
+                while not os.path.exists(flag) and time.time() - t_wait < 900:
+                    time.sleep(0.25)
     finally:
         if world > 1:
             import torch.distributed as dist
