@@ -228,9 +228,17 @@ def hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, batch):
                 for j in range(1, len(C4_L_VEC)):
                     worst = max(worst, float(np.max(np.abs(coef[0][y][p][j] - one[0][y][p][j])) / np.max(np.abs(one[0][y][p][j]))))
         out["beta_max_rel_diff_vs_1gpu_lambda_gt_0"] = worst
-    if rank != 0:
-        return out
-    # CPU arm on a bounded sample, extrapolated linearly (date-steps and refits are independent): numpy oracle, all BLAS threads
+    out["_sizes"] = (len(months), len(years))
+    return out
+
+
+def hp_grid_cpu_arm(out):
+    """CPU arm of hp_grid on a bounded sample, extrapolated linearly (date-steps and refits are independent): numpy oracle, all
+    BLAS threads.  Rank 0 only, AFTER every collective of the run (the other ranks sleep meanwhile)."""
+    syn = importlib.import_module(PKG + ".synthetic")
+    n_months, n_years = out.pop("_sizes")
+    months, years = range(n_months), range(n_years)
+    rng = np.random.default_rng(306)
     import pfml_oracle as O
     use_all_host_threads()
     small = make_bench_panel(syn, 10, 305)
@@ -618,7 +626,7 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.empty_cache()
 
     # ---- hp-grid wall-time: the whole C3 + C4 pipeline at N GPUs (all ranks take part) ---------------------
-    hp = hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, B) if not args.no_hp_grid else None
+    hp = hp_grid_pipeline_walltime(torch, dist, dev, comm, rank, world, B) if not args.no_hp_grid else None     # GPU part (all ranks)
     c5 = c5_universe(torch, dist, dev, lib, rank, world) if not args.no_hp_grid else None
     if comm is not None:
         comm.close()
@@ -675,6 +683,8 @@ def run_ours(args, rank, world, local_rank):
                                        "unit": "TFLOP/s", "frac": stages["denom"]["algorithmic_tflops"] / peak,
                                        "note": "whole a9 stage (graded contraction): stacked factor GEMMs on the DMMA pipe, two symmetric "
                                                "INT8 contractions, their operand slicing and the finish kernel with the fused window sums"}
+    if hp is not None:
+        hp_grid_cpu_arm(hp)
     hb = hbm_rows(torch, dev, lib) if world == 1 else None
     cpu_v, cpu_n, cpu_dt = cpu_dates_per_sec(syn)
     out = {
