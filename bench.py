@@ -647,10 +647,17 @@ def run_ours(args, rank, world, local_rank):
         probe[nm] = {"tops": tops.value, "nominal_clk_per_mma": clk.value} if rc == 0 else {"error": rc}
     int8_peak = probe["pipe_peak_M128_N256_A_in_TMEM"].get("tops", 0.0)
     n_pairs = 28
-    # the kernel's own instruction mix per 32-byte k slab: 18 products with A in TMEM, 10 with both operands in shared memory
+    # the kernel's own instruction stream per 32-byte k slab (three tcgen05.cp of A digits, 18 products with A in TMEM, 10 with
+    # both operands in shared memory), issued back to back on resident operands: the ceiling of THIS decomposition
     mix = None
-    if "tops" in probe["kernel_shape_N64_A_in_TMEM"] and "tops" in probe["kernel_shape_N64_SS"]:
-        mix = 28.0 / (18.0 / probe["kernel_shape_N64_A_in_TMEM"]["tops"] + 10.0 / probe["kernel_shape_N64_SS"]["tops"])
+    clk_s, tops_s = C.c_double(), C.c_double()
+    if lib.pfml_int8_pipe_probe(4096, 0, C.byref(clk_s), C.byref(tops_s)) == 0:
+        mix = tops_s.value
+        probe["kernel_k_slab_stream"] = {"tops": tops_s.value, "nominal_clk_per_k_slab": clk_s.value}
+        c1, t1 = C.c_double(), C.c_double()
+        if lib.pfml_int8_pipe_probe(4096, 1, C.byref(c1), C.byref(t1)) == 0:
+            probe["k_slab_stream_with_tcgen05_st_stagers"] = {"tops": t1.value, "nominal_clk_per_k_slab": c1.value,
+                                                              "note": "A digits 0..3 staged to TMEM by four extra warps instead of tcgen05.cp: no faster"}
     off = official_flops_per_date()
     k_emu = names.index("emu_i8_gemm")
     emu_ms = pms[k_emu] / args.steps
@@ -731,10 +738,12 @@ def run_ours(args, rank, world, local_rank):
                      "peak_source": "measured in this run: pfml_int8_mma_probe, back-to-back tcgen05.mma.kind::i8 M=128 N=256 K=32 with A "
                                     "in TMEM on all SMs (%.0f TOPS) / 28 digit products per FP64 product" % int8_peak,
                      "int8_probe": probe,
-                     "frac_of_instruction_mix_ceiling": (achieved * n_pairs / mix) if mix else None,
-                     "instruction_mix_ceiling_note": "the kernel issues M=128 N=64 K=32 (7 int32 accumulators x 64 columns fill TMEM): "
-                                                     "18 products per k slab with A in TMEM, 10 from shared memory; harmonic mean of the "
-                                                     "two probed rates = %s TOPS" % (("%.0f" % mix) if mix else "n/a"),
+                     "frac_of_instruction_stream_ceiling": (achieved * n_pairs / mix) if mix else None,
+                     "executed_frac_of_instruction_stream_ceiling": (pfl[k_emu] / args.steps / (emu_ms * 1e-3) * 1e-12 * n_pairs / mix) if mix else None,
+                     "instruction_stream_ceiling_note": "the kernel issues M=128 N=64 K=32 (7 int32 accumulators x 64 columns fill TMEM); its "
+                                                        "per-k-slab stream (3 tcgen05.cp + 18 products with A in TMEM + 10 from shared memory) "
+                                                        "issued back to back on resident operands measures %s TOPS (pfml_int8_pipe_probe); "
+                                                        "`executed_...` counts the padded flops actually issued" % (("%.0f" % mix) if mix else "n/a"),
                      "vs_cublas_dgemm_peak": achieved / peak_fp64, "cublas_dgemm_peak_tflops": peak_fp64,
                      "algorithmic_flops_per_step": emu_alg, "executed_padded_flops_per_step": pfl[k_emu] / args.steps,
                      "launch_ms_avg": emu_ms / max(emu_launches, 1.0),

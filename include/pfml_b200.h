@@ -322,6 +322,11 @@ int pfml_percentile_rank(const double* X, int T, int N, int F, int impute_half, 
  * tops = 1e-12 * int8 multiply-adds * 2 per second over all SMs; clk_per_mma (may be NULL) at the nominal maximum SM
  * clock.  Allocates one int on the device; synchronises. */
 int pfml_int8_mma_probe(int n, int iters, int ts_form, double* tops, double* clk_per_mma);
+/* The instruction stream of ONE 32-byte k slab of the emulated GEMM (7 accumulators of 64 columns, 28 digit products),
+ * repeated `iters` times per SM on resident operands: mode 0 = the production mix (three tcgen05.cp copies of A digits, 18
+ * products with A in TMEM, 10 with A in shared memory); mode 1 = A digits 0..3 moved to TMEM by tcgen05.st from four stager
+ * warps, double-buffered (22 + 6 products, no copy in the tensor queue).  clk_per_slab at the nominal maximum SM clock. */
+int pfml_int8_pipe_probe(int iters, int mode, double* clk_per_slab, double* tops);
 
 /* Device-time accounting with CUDA events (used by bench.py for the live roofline): enable, run, collect.
  * pfml_prof_collect synchronises the device, fills ms/flops/launches [n_tags] and clears the log.

@@ -125,6 +125,7 @@ SIGNATURES = {
     "pfml_unpack_upper": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "pfml_unpack_reals": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "pfml_percentile_rank": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "pfml_int8_pipe_probe": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "pfml_int8_mma_probe": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "pfml_prof_enable": (None, [C.c_int]),
     "pfml_prof_ntags": (C.c_int, []),

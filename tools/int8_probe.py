@@ -12,3 +12,9 @@ for ts in (0, 1):
             t, c = C.c_double(), C.c_double()
             rc = lib.pfml_int8_mma_probe(n, 8192, ts | (nacc << 8), C.byref(t), C.byref(c))
             print("M=128 N=%3d K=32 %s accumulators=%d: rc=%d %.0f TOPS, %.1f nominal clk/MMA (ideal %.0f)" % (n, "TS" if ts else "SS", nacc, rc, t.value, c.value, 128 * n * 32 * 2 / 16384.0), flush=True)
+
+for mode in (0, 1):
+    c, t = C.c_double(), C.c_double()
+    rc = lib.pfml_int8_pipe_probe(4096, mode, C.byref(c), C.byref(t))
+    print("k-slab stream mode %d (%s): rc=%d %.0f nominal clk per slab, %.0f TOPS" % (mode, "cp mix 18 TS + 10 SS" if mode == 0 else "tcgen05.st stagers 22 TS + 6 SS", rc, c.value, t.value), flush=True)
+    if rc: print(lib.pfml_last_error())
