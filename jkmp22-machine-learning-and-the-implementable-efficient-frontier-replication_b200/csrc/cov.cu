@@ -176,13 +176,26 @@ xs_ols_kernel(int K, const double* __restrict__ X, const double* __restrict__ y,
 }
 
 // ---- a16: one CTA per calc date -------------------------------------------------------------------
+// weighted_cor_wt (weights w_cor) and the diagonal of weighted_cov_wt (weights w_var) over the window of the calc date,
+// General_functions.py:745-835, then sd cor sd ("Estimate Covariance Matrix.py":316-320).  The normalised weights
+// w_i / sum(w) live in shared memory (2 x obs doubles, dynamic).  The window (L2-resident: the whole D x K matrix is
+// 1 MB) is streamed twice through 128-row chunks in shared memory, row stride padded to 28: pass 1 the weighted means,
+// pass 2 the centred weighted Gram matrix in 4 x 4 register tiles (28 lower-triangle tiles on 28 lanes of each of the
+// 8 warps, warp w takes rows i = w (mod 8): four 16-byte loads feed 16 FMAs) plus the w_var-weighted variances on
+// lanes 0 .. K-1.  Partial results of the 8 warps are added in warp order (deterministic).
 __global__ void __launch_bounds__(256)
 wcov_wcor_kernel(int K, int obs, const double* __restrict__ F, const int* __restrict__ end_idx, const double* __restrict__ w_cor,
                  const double* __restrict__ w_var, double scale, double* __restrict__ out) {
-  constexpr int S = KC + 1;
-  __shared__ double mu_c[KC], mu_v[KC], cov[KC][S], var_v[KC];
-  __shared__ double red[4][256 / 32];
-  __shared__ double sums[4];     // sum w_cor, sum w_var, sum wn_cor^2, sum wn_var^2
+  constexpr int S = KC + 1, CH = 128;
+  __shared__ __align__(16) double Xc[CH * KA];
+  __shared__ double mu_c[KA], mu_v[KA], cov[KC][S], var_v[KC];
+  __shared__ double red[4][8];
+  __shared__ double part[8][KA][2];     // per-warp partial sums of pass 1, then of the variances
+  __shared__ double sums[4];            // sum w_cor, sum w_var, sum wn_cor^2, sum wn_var^2
+  extern __shared__ double s_wn[];      // [obs] normalised w_cor, [obs] normalised w_var, then the 8 partial Gram matrices
+  double* wnc = s_wn;
+  double* wnv = s_wn + obs;
+  double* Gp = s_wn + 2 * obs;          // [8][KA][KA + 1]
   const int cd = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int e = end_idx[cd];
   const int t = (e + 1) < obs ? (e + 1) : obs;
@@ -202,7 +215,7 @@ wcov_wcor_kernel(int K, int obs, const double* __restrict__ F, const int* __rest
   if (tid < 2) { double v = 0; for (int k = 0; k < 8; k++) v += red[tid][k]; sums[tid] = v; }
   __syncthreads();
   const double swc = sums[0], swv = sums[1];
-  for (int i = tid; i < t; i += 256) { const double a = wc[i] / swc, b = wv[i] / swv; s[2] += a * a; s[3] += b * b; }
+  for (int i = tid; i < t; i += 256) { const double a = wc[i] / swc, b = wv[i] / swv; wnc[i] = a; wnv[i] = b; s[2] += a * a; s[3] += b * b; }
   for (int q = 2; q < 4; q++) {
     double v = s[q];
 #pragma unroll
@@ -211,49 +224,102 @@ wcov_wcor_kernel(int K, int obs, const double* __restrict__ F, const int* __rest
   }
   __syncthreads();
   if (tid >= 2 && tid < 4) { double v = 0; for (int k = 0; k < 8; k++) v += red[tid][k]; sums[tid] = v; }
-  // weighted means: warp w handles factors w, w+8, ...
-  for (int c = warp; c < K; c += 8) {
-    double a = 0, b = 0, na = 0, nb = 0;
-    for (int i = lane; i < t; i += 32) {
-      const double x = F[(first + i) * K + c];
-      const double wa = wc[i] / swc, wb = wv[i] / swv;
-      a += wa * x; b += wb * x; na += wa; nb += wb;
+  for (int i = tid; i < CH * KA; i += 256) Xc[i] = 0.0;      // padding columns stay zero
+  __syncthreads();
+  const float invK = 1.0f / (float)K;
+  auto stage = [&](int i0, int nr) {                         // rows i0 .. i0 + nr - 1 of the window -> Xc (coalesced flat reads)
+    const double* src = F + (first + i0) * K;
+    for (int q = tid; q < nr * K; q += 256) {
+      const int r = (int)(((float)q + 0.5f) * invK), c = q - r * K;
+      Xc[r * KA + c] = src[q];
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o);
-      na += __shfl_xor_sync(0xffffffffu, na, o); nb += __shfl_xor_sync(0xffffffffu, nb, o);
-    }
-    if (lane == 0) { mu_c[c] = a / na; mu_v[c] = b / nb; }      // np.average divides by the weight sum
+  };
+  // ---- pass 1: weighted means (np.average divides by the weight sum) -----------------------------------------
+  double a1 = 0, b1 = 0, na = 0, nb = 0;
+  for (int i0 = 0; i0 < t; i0 += CH) {
+    const int nr = t - i0 < CH ? t - i0 : CH;
+    __syncthreads();
+    stage(i0, nr);
+    __syncthreads();
+    if (lane < KA)
+      for (int i = warp; i < nr; i += 8) {
+        const double x = Xc[i * KA + lane], wa = wnc[i0 + i], wb = wnv[i0 + i];
+        a1 += wa * x; b1 += wb * x; na += wa; nb += wb;
+      }
+  }
+  if (lane < KA) { part[warp][lane][0] = a1; part[warp][lane][1] = b1; }
+  if (lane == 0) { red[0][warp] = na; red[1][warp] = nb; }
+  __syncthreads();
+  if (tid < KA) {
+    double a = 0, b = 0, sa = 0, sb = 0;
+    for (int w = 0; w < 8; w++) { a += part[w][tid][0]; b += part[w][tid][1]; sa += red[0][w]; sb += red[1][w]; }
+    mu_c[tid] = a / sa; mu_v[tid] = b / sb;
   }
   __syncthreads();
   const double den_c = 1.0 - sums[2], den_v = 1.0 - sums[3];
-  // centred, weighted products: pair (a, c<=a) per warp-iteration
-  for (int pr = warp; pr < K * (K + 1) / 2 + K; pr += 8) {
-    double acc = 0.0;
-    if (pr < K * (K + 1) / 2) {
-      int a = 0, rem = pr;
-      while (rem > a) { rem -= a + 1; a++; }
-      const int c = rem;
-      for (int i = lane; i < t; i += 32) {
-        const double wn = wc[i] / swc;
-        const double* row = F + (first + i) * K;
-        acc += wn * (row[a] - mu_c[a]) * (row[c] - mu_c[c]);
-      }
+  // ---- pass 2: centred weighted Gram matrix (w_cor) in 4 x 4 tiles, variances (w_var) on lanes < K -----------------
+  int ta = 0, tc = 0;
+  {
+    int l = lane;
+    while (l > ta) { l -= ta + 1; ta++; }
+    tc = l;
+  }
+  const bool active = lane < 28;
+  double acc[4][4];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-      if (lane == 0) { cov[a][c] = acc / den_c; cov[c][a] = acc / den_c; }
-    } else {
-      const int a = pr - K * (K + 1) / 2;
-      for (int i = lane; i < t; i += 32) {
-        const double wn = wv[i] / swv;
-        const double xc = F[(first + i) * K + a] - mu_v[a];
-        acc += wn * xc * xc;
-      }
+  for (int u = 0; u < 4; u++)
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-      if (lane == 0) var_v[a] = acc / den_v;
+    for (int v = 0; v < 4; v++) acc[u][v] = 0.0;
+  double ma[4], mc[4];
+#pragma unroll
+  for (int u = 0; u < 4; u++) { ma[u] = active ? mu_c[4 * ta + u] : 0.0; mc[u] = active ? mu_c[4 * tc + u] : 0.0; }
+  const double mv = lane < K ? mu_v[lane] : 0.0;
+  double vacc = 0.0;
+  for (int i0 = 0; i0 < t; i0 += CH) {
+    const int nr = t - i0 < CH ? t - i0 : CH;
+    __syncthreads();
+    stage(i0, nr);
+    __syncthreads();
+    for (int i = warp; i < nr; i += 8) {
+      const double wn = wnc[i0 + i];
+      if (active) {
+        const double2* pa = reinterpret_cast<const double2*>(Xc + i * KA + 4 * ta);
+        const double2* pc = reinterpret_cast<const double2*>(Xc + i * KA + 4 * tc);
+        const double2 a01 = pa[0], a23 = pa[1], c01 = pc[0], c23 = pc[1];
+        const double av[4] = {wn * (a01.x - ma[0]), wn * (a01.y - ma[1]), wn * (a23.x - ma[2]), wn * (a23.y - ma[3])};
+        const double cv[4] = {c01.x - mc[0], c01.y - mc[1], c23.x - mc[2], c23.y - mc[3]};
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+#pragma unroll
+          for (int v = 0; v < 4; v++) acc[u][v] += av[u] * cv[v];
+      }
+      if (lane < K) {
+        const double xc = Xc[i * KA + lane] - mv;
+        vacc += wnv[i0 + i] * xc * xc;
+      }
     }
+  }
+  auto Gat = [&](int w, int r, int c) -> double& { return Gp[(w * KA + r) * (KA + 1) + c]; };
+  if (active) {
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+#pragma unroll
+      for (int v = 0; v < 4; v++) Gat(warp, 4 * ta + u, 4 * tc + v) = acc[u][v];
+  }
+  if (lane < KA) part[warp][lane][0] = vacc;
+  __syncthreads();
+  for (int q = tid; q < K * KA; q += 256) {
+    const int a = q / KA, c = q % KA;
+    if (c <= a) {
+      double v = 0.0;
+      for (int w = 0; w < 8; w++) v += Gat(w, a, c);
+      cov[a][c] = v / den_c; cov[c][a] = v / den_c;
+    }
+  }
+  if (tid < K) {
+    double v = 0.0;
+    for (int w = 0; w < 8; w++) v += part[w][tid][0];
+    var_v[tid] = v / den_v;
   }
   __syncthreads();
   // cov_est = sd (cor) sd with unit-diagonal cor, times `scale` (x 21 at :476)
@@ -350,13 +416,20 @@ int pfml_xs_ols_daily(const double* X, const double* y, const long* day_ptr, int
 
 int pfml_wcov_wcor(const double* fct_ret, const int* end_idx, int n_calc, int K, int obs, const double* w_cor,
                    const double* w_var, double scale, double* cov_out, void* stream) {
-  if (!fct_ret || !end_idx || !w_cor || !w_var || !cov_out || n_calc <= 0 || K <= 0 || K > KC || obs <= 0) {
-    set_error("pfml_wcov_wcor: null/empty argument or K > %d", KC);
+  if (!fct_ret || !end_idx || !w_cor || !w_var || !cov_out || n_calc <= 0 || K <= 0 || K > KA || obs <= 0) {
+    set_error("pfml_wcov_wcor: null/empty argument or K > %d", KA);
     return -1;
   }
   cudaStream_t s = (cudaStream_t)stream;
   ProfScope ps(T_COV, s);
-  wcov_wcor_kernel<<<n_calc, 256, 0, s>>>(K, obs, fct_ret, end_idx, w_cor, w_var, scale, cov_out);
+  const size_t smem = (2 * (size_t)obs + 8 * KA * (KA + 1)) * sizeof(double);
+  constexpr size_t kMaxDyn = 176 * 1024;                  // + 41 KB of static shared memory stays below the 227 KB of a CTA
+  if (smem > kMaxDyn) {
+    set_error("pfml_wcov_wcor: window of %d observations exceeds the shared-memory weights (max 7900)", obs);
+    return -2;
+  }
+  PFML_CONFIG_ONCE(wcov_wcor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDyn);
+  wcov_wcor_kernel<<<n_calc, 256, smem, s>>>(K, obs, fct_ret, end_idx, w_cor, w_var, scale, cov_out);
   PFML_CHECK_LAUNCH();
   return 0;
 }
