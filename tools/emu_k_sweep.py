@@ -5,7 +5,9 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 PKG = "jkmp22-machine-learning-and-the-implementable-efficient-frontier-replication_b200"
-lib = importlib.import_module(PKG + "._lib").load()
+_L = importlib.import_module(PKG + "._lib")
+if os.environ.get("PFML_LIB"): _L.LIB_PATH = os.environ["PFML_LIB"]
+lib = _L.load()
 dev = torch.device("cuda:0")
 nt = lib.pfml_prof_ntags()
 names = [lib.pfml_prof_tag_name(i).decode() for i in range(nt)]
