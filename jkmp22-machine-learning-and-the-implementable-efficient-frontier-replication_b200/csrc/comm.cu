@@ -109,6 +109,11 @@ int pfml_comm_init(const void* id128, int rank, int world, int device, void** co
     return -1;
   }
   PFML_TRY(need_nccl("pfml_comm_init"));
+  struct Restore {                     // NCCL binds the communicator to the current device; the caller's device is put back
+    int prev = -1;
+    Restore() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+    ~Restore() { if (prev >= 0) cudaSetDevice(prev); }
+  } restore;
   PFML_CUDA_OK(cudaSetDevice(device));
   Comm* c = new Comm;
   c->rank = rank; c->world = world; c->device = device;
