@@ -802,7 +802,7 @@ using namespace pfml;
 
 extern "C" {
 
-const char* pfml_version(void) { return "pfml_b200 0.2 (sm_100a, FP64 DMMA + INT8 tcgen05 emulation)"; }
+const char* pfml_version(void) { return "pfml_b200 0.3 (sm_100a, FP64 DMMA + INT8 tcgen05 emulation, NCCL exchange)"; }
 const char* pfml_last_error(void) { return last_error(); }
 
 int pfml_padded_n(int n_max) { return (int)round_up(n_max < 1 ? 1 : n_max, BASE); }
