@@ -325,7 +325,7 @@ def hbm_rows(torch, dev, lib):
     ptr = lambda t: C.c_void_p(t.data_ptr())
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
-    def timed(fn, reps=5):
+    def timed(fn, reps=int(os.environ.get("PFML_HBM_REPS", "5"))):
         fn(); fn()
         best = 1e30
         for _ in range(reps):
